@@ -1,0 +1,239 @@
+/*
+ * rtc.h — C ABI of the B200-native render path for zig_raytracing_contest.
+ *
+ * This is the drop-in boundary for the reference's one data-parallel hot path:
+ *     try scene.render(threads, camera, img);          (src/main.zig:126)
+ *     pub fn render(self: Scene, threads: []std.Thread,
+ *                   camera: Camera, img: []RGB) !void  (src/stage3.zig:247)
+ * The reference's only existing FFI seam is Zig -> C for stb
+ * (src/c.zig:2-5, src/c_impl.c:1-5, linked by build.zig:29-48); this header is
+ * what a maintainer adds to that @cImport block.
+ *
+ * Conventions
+ *   - plain C, explicit layouts, no Zig @Vector / auto-layout structs cross the ABI;
+ *   - every function returns 0 on success, a nonzero rtc_status otherwise, and
+ *     leaves a message retrievable with rtc_last_error() (thread-local);
+ *   - the caller owns every host pointer it passes; the library copies at
+ *     rtc_scene_create and never retains host pointers;
+ *   - no CPU fallback: every entry point that computes fails with
+ *     RTC_ERR_NO_DEVICE when no sm_100 device is usable.
+ */
+#ifndef RTC_H_
+#define RTC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTC_ABI_VERSION 1u
+
+typedef enum rtc_status {
+    RTC_OK = 0,
+    RTC_ERR_INVALID_ARGUMENT = 1,
+    RTC_ERR_NO_DEVICE = 2,
+    RTC_ERR_CUDA = 3,
+    RTC_ERR_OUT_OF_MEMORY = 4,
+    RTC_ERR_IO = 5,
+    RTC_ERR_FORMAT = 6,      /* glTF / config.json contract violation */
+    RTC_ERR_UNSUPPORTED = 7
+} rtc_status;
+
+/* ---- data the hot path consumes ------------------------------- */
+
+/* linalg.Grid (src/linalg.zig:407-410): bbox + resolution + cell_size = size/res. */
+typedef struct rtc_grid {
+    float    bbox_min[3];
+    float    bbox_max[3];
+    uint32_t resolution[3];
+    float    cell_size[3];
+} rtc_grid;
+
+/* stage3.Cell (src/stage3.zig:131-134): [begin,end) into the baked triangle arrays. */
+typedef struct rtc_cell {
+    uint32_t begin;
+    uint32_t end;
+} rtc_cell;
+
+/* linalg.Triangle {v0,e1,e2} (src/linalg.zig:683-694). Vec3 = @Vector(3,f32) is
+ * 16 bytes in memory, so the reference's record is 48 bytes; [3] of each row is
+ * ignored on input. */
+typedef struct rtc_tri_pos {
+    float v0[4];
+    float e1[4];
+    float e2[4];
+} rtc_tri_pos;
+
+/* stage3.Triangle.Data (src/stage3.zig:42-50) restated with a fixed layout, plus the
+ * source-triangle id that stage2's indices[] holds (src/stage2.zig:151-152) and the
+ * reference drops at bake time. src_tri is what parity tests compare. */
+typedef struct rtc_tri_data {
+    float    normal[3][3];   /* per vertex, world space, as loaded (not renormalised) */
+    float    texcoord[3][2];
+    uint32_t material;
+    uint32_t src_tri;
+} rtc_tri_data;
+
+/* stage3.Texture(T) (src/stage3.zig:82-123). channels = 3 (Vec3 texel, tightly packed
+ * rgb floats, linear light, factor pre-multiplied) or 1 (f32 texel). */
+typedef struct rtc_texture {
+    const float* texels;     /* w*h*channels floats, row-major, row 0 first */
+    int32_t w, h;
+    int32_t u_min, u_max;    /* clamp range applied before the floored mod */
+    int32_t v_min, v_max;
+    int32_t channels;
+} rtc_texture;
+
+/* stage3.Material (src/stage3.zig:125-129). */
+typedef struct rtc_material {
+    rtc_texture base_color;    /* channels = 3 */
+    rtc_texture emissive;      /* channels = 3 */
+    rtc_texture transparency;  /* channels = 1; value is the scatter probability */
+} rtc_material;
+
+/* stage3.Scene (src/stage3.zig:136-142) after stage2.bakeInto (src/stage2.zig:137-164). */
+typedef struct rtc_scene_desc {
+    rtc_grid            grid;
+    const rtc_cell*     cells;        /* prod(resolution) entries, x fastest (linalg.zig:429) */
+    uint64_t            num_cells;
+    const rtc_tri_pos*  tri_pos;      /* num_tris baked (duplicated, cell-ordered) records */
+    const rtc_tri_data* tri_data;     /* num_tris records, same order */
+    uint64_t            num_tris;
+    const rtc_material* materials;
+    uint32_t            num_materials;
+    uint32_t            num_src_tris; /* 1 + max(src_tri); 0 = derive */
+} rtc_scene_desc;
+
+/* stage3.Camera (src/stage3.zig:19-35). right/up are per-pixel steps; up points DOWN
+ * the image (src/stage1.zig:354-355) so row 0 is the top row. */
+typedef struct rtc_camera {
+    uint32_t w, h;
+    float origin[3];
+    float lower_left_corner[3];
+    float right[3];
+    float up[3];
+} rtc_camera;
+
+/* Render modes. The reference has exactly one (PATH); PRIMARY is the deterministic
+ * slice used for the hit-id parity gate. */
+enum {
+    RTC_MODE_PATH = 0,     /* renderWorker + traceRayRecursive (src/stage3.zig:188-245) */
+    RTC_MODE_PRIMARY = 1   /* one ray through each pixel centre, depth 1, no RNG:
+                              hit -> emissive, miss -> sky; fills rtc_aux hit buffers */
+};
+
+/* Traversal selector (results are identical except in exact-t ties). */
+enum {
+    RTC_ACCEL_GRID = 0     /* uniform grid + 3D-DDA in the reference's cell order */
+};
+
+/* Arithmetic contract. EXACT: no FMA contraction anywhere the reference has separate
+ * mul/add, IEEE div/sqrt — bit-identical to the oracle. FAST: same kernels compiled
+ * with contraction allowed; hit ids may differ on near-tie pixels only. */
+enum {
+    RTC_MATH_EXACT = 0,
+    RTC_MATH_FAST = 1
+};
+
+/* main.Config (src/main.zig:56-61) + what the CLI adds. num_samples/max_bounce are the
+ * two hot-loop trip counts (src/stage3.zig:237,239). */
+typedef struct rtc_params {
+    uint16_t num_samples;    /* samples rendered by THIS call */
+    uint16_t max_bounce;
+    uint32_t mode;           /* RTC_MODE_* */
+    uint64_t seed;           /* counter-RNG key; stream = (seed, pixel, sample, draw) */
+    uint32_t sample_offset;  /* index of this call's first sample in the frame (sample sharding) */
+    uint32_t total_samples;  /* frame total used for the 1/S scale; 0 = num_samples */
+    uint32_t accel;          /* RTC_ACCEL_* */
+    uint32_t math;           /* RTC_MATH_* */
+    uint32_t tile_rank;      /* tile sharding: this call renders 8x4-pixel tiles t with  */
+    uint32_t tile_world;     /* (t / tile_group) % tile_world == tile_rank; 0/1 = all    */
+    uint32_t collect_stats;  /* nonzero: run the instrumented kernels, fill rtc_aux.stats */
+    uint32_t reserved;
+} rtc_params;
+
+/* Counters behind SURVEY §8(d)'s bytes-per-ray figure. */
+typedef struct rtc_stats {
+    uint64_t rays;           /* traceRay invocations (camera + bounce + alpha continuation) */
+    uint64_t cells_visited;  /* 8-byte Cell records fetched                                  */
+    uint64_t tris_tested;    /* 48-byte {v0,e1,e2} records fetched                           */
+    uint64_t hits_shaded;    /* hits that fetched triangle data + 3 textures                 */
+    uint64_t paths;          /* camera rays                                                  */
+    double   kernel_ms;      /* device time of the render kernels of the last call           */
+} rtc_stats;
+
+/* Optional extra outputs (any pointer may be NULL). Host pointers. */
+typedef struct rtc_aux {
+    uint32_t*  hit_id;    /* w*h: source-triangle id of the primary hit, 0xFFFFFFFF = miss (PRIMARY) */
+    float*     hit_tuv;   /* w*h*3: t,u,v of the primary hit (PRIMARY)                               */
+    float*     radiance;  /* w*h*3: linear mean radiance before toRGB                                */
+    rtc_stats* stats;
+} rtc_aux;
+
+typedef struct rtc_scene rtc_scene;   /* opaque; owns device memory */
+
+/* ---- the render path ------------------------------------------------------------- */
+
+/* Uploads a baked scene (what the reference holds in `scene` at src/main.zig:118).
+ * device < 0 selects the current CUDA device. */
+int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
+
+void rtc_scene_destroy(rtc_scene* scene);
+
+/* Replaces scene.render(threads, camera, img) (src/main.zig:126, src/stage3.zig:247).
+ * rgb_out: w*h*3 bytes, row 0 = top, the exact buffer stbi_write_png is handed at
+ * src/main.zig:130-135. Blocking, like the reference (threads joined at stage3.zig:253). */
+int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
+               uint8_t* rgb_out, rtc_aux* aux);
+
+/* ---- device-resident pieces of the same path (multi-GPU plumbing, benchmarking) --- */
+
+/* Adds this call's samples into d_accum (device, w*h float4: rgb sum + sample count),
+ * asynchronously on `stream` (a cudaStream_t, NULL = default stream). */
+int rtc_render_accumulate(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
+                          void* d_accum, void* stream);
+
+/* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242, src/linalg.zig:150-159):
+ * d_accum (w*h float4) -> d_rgb (w*h*3 bytes) and/or d_radiance (w*h*3 floats). */
+int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples,
+                void* d_rgb, void* d_radiance, int device, void* stream);
+
+/* Fetches and clears the ray/traversal counters accumulated on the scene's device
+ * since the last call (synchronises the device). */
+int rtc_scene_stats(rtc_scene* scene, rtc_stats* out);
+
+/* ---- stage2 as the path's producer ------------------------------ */
+
+/* Geometry.build + bakeInto (src/stage2.zig:131-164) from a triangle soup:
+ * positions = num_tris*9 floats (3 world-space vertices), data = num_tris records whose
+ * src_tri is ignored on input. Outputs are library-owned and live until rtc_geometry_free. */
+typedef struct rtc_geometry {
+    rtc_grid      grid;
+    rtc_cell*     cells;
+    uint64_t      num_cells;
+    rtc_tri_pos*  tri_pos;
+    rtc_tri_data* tri_data;
+    uint64_t      num_tris;      /* baked count (sum over cells) */
+    uint32_t      num_src_tris;
+    uint32_t      empty_cells;
+    uint32_t      min_tris, max_tris;   /* over non-empty cells (src/stage2.zig:76-100) */
+    void*         owner;
+} rtc_geometry;
+
+int  rtc_geometry_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
+                        const uint32_t grid_resolution[3], rtc_geometry* out);
+void rtc_geometry_free(rtc_geometry* g);
+
+/* ---- misc ------------------------------------------------------------------------ */
+
+const char* rtc_last_error(void);
+uint32_t    rtc_abi_version(void);
+/* Number of usable sm_100 devices (0 when none; never an error). */
+int         rtc_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTC_H_ */
