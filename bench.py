@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s and ms/frame of the render path on N B200s, beside the CPU restatement.
+
+A step = one frame of the workload (default: BASELINE.json configs[2], the path-traced 1920x1080
+64 spp render; configs[0]/[1] are ~2 M-ray primary-visibility parity cases, not bench lines).
+N > 1 (torchrun, one rank per GPU): the scene is replicated, every rank renders its own sample
+range of the same frame (weak scaling: 64 spp per GPU), the float4 accumulators are summed to
+rank 0 with one NCCL reduce and rank 0 resolves to RGB8 (SURVEY §8(e) partitioning B).
+
+  value : rays traced by all ranks / device time (CUDA events on the launch stream, max over ranks),
+          scene resident in HBM
+  e2e   : the same through the blocking C-ABI call rtc_render() with host camera/params in and the
+          host RGB8 frame out (D2H inside the timed region)
+  --impl reference : the CPU restatement of the reference (oracle/, all host threads) on a bounded
+          sample of the same frame
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (scene, scene kwargs, grid, height, spp, max_bounce)
+    "cfg3_atrium_1080p_64spp": ("atrium", {}, (128, 128, 128), 1080, 64, 4),
+    "cfg4_terrain5M_4k_256spp": ("terrain", {"num_tris": 5_000_000}, (128, 128, 128), 2160, 256, 4),
+    "smoke_cornell_360p_8spp": ("cornell", {}, (32, 32, 32), 360, 8, 4),
+}
+DEFAULT_WORKLOAD = "cfg3_atrium_1080p_64spp"
+SEED = 1
+
+
+def build_workload(name):
+    from zig_raytracing_contest_b200 import rtc, scenes
+    scene_name, kw, grid, height, spp, bounce = WORKLOADS[name]
+    spec = scenes.SCENES[scene_name](**kw)
+    t0 = time.time()
+    geo = rtc.Geometry(spec.positions, spec.tri_data, grid)
+    build_s = time.time() - t0
+    cam = spec.camera(height=height)
+    return spec, geo, cam, spp, bounce, build_s
+
+
+def sample_bands(h, n_rows, bands=8):
+    """n_rows rows of the frame as `bands` evenly spaced contiguous bands -> [(y0,y1)]."""
+    bands = max(1, min(bands, n_rows))
+    per = max(1, n_rows // bands)
+    out = []
+    for b in range(bands):
+        y0 = int((b + 0.5) * h / bands - per / 2)
+        y0 = max(0, min(h - per, y0))
+        out.append((y0, y0 + per))
+    return out
+
+
+def cpu_render_sample(desc, cam, spp, bounce, n_rows, threads):
+    """Times the oracle's Scene.render on a bounded sample of rows. Returns (rays, seconds, rows)."""
+    from oracle import oracle
+    from zig_raytracing_contest_b200 import rtc
+    prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED)
+    rays, secs, rows = 0, 0.0, 0
+    for y0, y1 in sample_bands(cam.h, n_rows):
+        t0 = time.perf_counter()
+        out = oracle.render(desc, cam, prm, num_threads=threads, rows=(y0, y1), want_radiance=False, want_stats=True)
+        secs += time.perf_counter() - t0
+        rays += out["stats"]["rays"]
+        rows += y1 - y0
+    return rays, secs, rows
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    from zig_raytracing_contest_b200 import rtc
+    spec, geo, cam, spp, bounce, _ = build_workload(args.workload)
+    desc, keep = rtc.make_scene_desc(geo, spec.materials)
+    threads = os.cpu_count() or 1
+    n_rows = args.cpu_rows
+    if n_rows <= 0:
+        rays, secs, rows = cpu_render_sample(desc, cam, spp, bounce, 8, threads)       # calibrate ~ to 8 s per step
+        n_rows = int(max(8, min(cam.h, rows * 8.0 / max(secs, 1e-3))))
+    for _ in range(args.warmup):
+        cpu_render_sample(desc, cam, spp, bounce, max(8, n_rows // 8), threads)
+    tot_rays, tot_secs, rows = 0, 0.0, 0
+    for _ in range(args.steps):
+        rays, secs, rows = cpu_render_sample(desc, cam, spp, bounce, n_rows, threads)
+        tot_rays += rays; tot_secs += secs
+    mrays = tot_rays / tot_secs / 1e6
+    frame_ms = tot_secs / args.steps * (cam.h / rows) * 1e3
+    sample = "%d of %d rows (%d evenly spaced bands), all %d spp, per step" % (rows, cam.h, len(sample_bands(cam.h, n_rows)), spp)
+    print(json.dumps({
+        "impl": "reference", "metric": "Mrays/s", "value": round(mrays, 4), "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(frame_ms, 2), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, spec, geo, cam, spp, bounce, max(1, args.gpus)),
+        "cpu_baseline": {"value": round(mrays, 4), "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample,
+                         "note": "C restatement of the Zig reference (no Zig toolchain on this box); ms_per_step is the sample extrapolated to the full frame"},
+        "e2e": {"value": round(mrays, 4), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(name, spec, geo, cam, spp, bounce, world):
+    return {"workload": name, "scene": spec.name, "source_triangles": spec.num_tris, "baked_triangles": geo.num_tris,
+            "grid": [int(x) for x in geo.grid.resolution], "width": int(cam.w), "height": int(cam.h),
+            "spp_per_gpu": spp, "spp_total": spp * world, "max_bounce": bounce, "seed": SEED,
+            "sharding": "sample ranges, scene replicated, NCCL reduce(sum) of float4 accumulators" if world > 1 else "none",
+            "l2": "flushed between timed steps by writing a 512 MiB buffer", "math": "exact (no FMA contraction)"}
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from zig_raytracing_contest_b200 import abi, rtc
+    if rtc.device_count() < 1:
+        raise SystemExit("bench.py: no sm_100 GPU visible and the render path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    spec, geo, cam, spp, bounce, build_s = build_workload(args.workload)
+    t0 = time.perf_counter()
+    scene = rtc.Scene(geo, spec.materials, device=local_rank)
+    upload_s = time.perf_counter() - t0
+    P = cam.w * cam.h
+    math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
+    total = spp * world
+    prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, sample_offset=rank * spp, total_samples=total, math=math)
+    acc = torch.zeros(P, 4, device=dev)
+    d_rgb = torch.zeros(P * 3, dtype=torch.uint8, device=dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(ev_k0=None, ev_k1=None):
+        acc.zero_()
+        if ev_k0: ev_k0.record()
+        scene.render_accumulate(cam, prm, acc.data_ptr(), stream)
+        if ev_k1: ev_k1.record()
+        if world > 1:
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            rtc.resolve(acc.data_ptr(), P, total, d_rgb.data_ptr(), None, device=local_rank, stream_ptr=stream)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    scene.stats()                                   # clears the ray counters
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    barrier()
+    with ClockSampler(local_rank) as clocks:
+        for k in range(args.steps):
+            flush.zero_()                           # evict the scene from the 126 MB L2 between steps
+            ev[k][0].record()
+            step(ev[k][1], ev[k][2])
+            ev[k][3].record()
+        barrier()
+    step_ms = sum(e[0].elapsed_time(e[3]) for e in ev)
+    kern_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    st = scene.stats()
+    t = torch.tensor([step_ms], device=dev, dtype=torch.float64)
+    r = torch.tensor([float(st["rays"]), float(st["paths"])], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(r, op=dist.ReduceOp.SUM)
+    step_ms = float(t[0]) / args.steps
+    rays_per_step = float(r[0]) / args.steps
+    value = rays_per_step / (step_ms * 1e-3) / 1e6
+
+    # ---- e2e: the blocking public call, host buffers, D2H of the frame inside the timed region ----
+    img = np.zeros((cam.h, cam.w, 3), np.uint8)
+    host_acc = torch.zeros(P * 3, dtype=torch.uint8).pin_memory() if world > 1 else None
+
+    def e2e_step():
+        if world == 1:
+            scene.render(cam, prm, img=img)
+        else:
+            step()
+            if rank == 0:
+                host_acc.copy_(d_rgb, non_blocking=True)
+                torch.cuda.synchronize()
+                img.reshape(-1)[:] = host_acc.numpy()
+    e2e_step()
+    barrier()
+    flush.zero_(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te[0])
+    e2e_val = rays_per_step / e2e_s / 1e6
+
+    out = None
+    if rank == 0:
+        # instrumented launch of the same frame: counts behind the algorithmic bytes
+        prm_s = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, sample_offset=0, total_samples=total,
+                                math=math, collect_stats=True)
+        acc.zero_(); torch.cuda.synchronize()
+        scene.stats()
+        scene.render_accumulate(cam, prm_s, acc.data_ptr(), stream)
+        cs = scene.stats()
+        algo_bytes = rtc.bytes_per_frame(cs, P)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        cfg = workload_config(args.workload, spec, geo, cam, spp, bounce, world)
+        cfg["math"] = "exact (no FMA contraction)" if math == abi.RTC_MATH_EXACT else "fast (FMA contraction)"
+        cfg["host_build_s"] = round(build_s, 3); cfg["scene_upload_s"] = round(upload_s, 3)
+        cfg["per_ray"] = {"cells": round(cs["cells_visited"] / cs["rays"], 2), "tris": round(cs["tris_tested"] / cs["rays"], 2),
+                          "bytes": round(algo_bytes / cs["rays"], 1), "rays_per_path": round(cs["rays"] / cs["paths"], 3)}
+        out = {
+            "metric": "Mrays/s", "value": round(value, 2), "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+            "e2e": {"value": round(e2e_val, 2), "unit": "Mrays/s", "ms_per_frame": round(e2e_s * 1e3, 3),
+                    "h2d_bytes_per_step": 56 + 48, "d2h_bytes_per_step": P * 3,
+                    "note": "rtc_render(): host camera+params in, host RGB8 frame out; scene resident (uploaded once, like the reference's bakeInto before render)"},
+            "gpu_launches": 2 * args.steps,
+            "kernel_ms": {"k_path": round(kern_ms, 3)},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 5), "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "algorithmic_bytes_per_launch": int(algo_bytes),
+                         "note": "k_path; bytes = 8/cell + 48/triangle test + 224/shaded hit + 3/pixel, counted by an instrumented launch of the same frame"},
+            "clocks": clocks.summary(),
+        }
+        if world == 1 and not args.no_cpu:
+            desc = scene.desc
+            threads = os.cpu_count() or 1
+            rays, secs, rows = cpu_render_sample(desc, cam, spp, bounce, 8, threads)
+            n_rows = int(max(8, min(cam.h, rows * args.cpu_seconds / max(secs, 1e-3))))
+            rays, secs, rows = cpu_render_sample(desc, cam, spp, bounce, n_rows, threads)
+            out["cpu_baseline"] = {"value": round(rays / secs / 1e6, 4), "unit": "Mrays/s", "cores": threads, "kind": "port",
+                                   "sample": "%d of %d rows (%d evenly spaced bands), all %d spp; %.1f s" % (rows, cam.h, len(sample_bands(cam.h, n_rows)), spp, secs),
+                                   "ms_per_frame_extrapolated": round(secs * cam.h / rows * 1e3, 1)}
+        print(json.dumps(out))
+    scene.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--math", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--cpu-rows", type=int, default=0, help="--impl reference: rows per step (0 = calibrate to ~8 s)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

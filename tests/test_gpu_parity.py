@@ -1,0 +1,159 @@
+"""Parity of the CUDA render path (through the C ABI) against the CPU oracle on the same seeded
+inputs. Bars: primary-ray hit ids and t,u,v bit-exact in the exact build; f32
+radiance bit-exact in the exact build (same counter RNG, same operation order); RGB8 within
+1 LSB (powf differs between libm and CUDA); fast build: hit ids equal except near-ties (fraction
+asserted), radiance within 1e-3 relative RMSE."""
+import numpy as np
+import pytest
+
+from zig_raytracing_contest_b200 import abi, rtc, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def setups(orc):
+    out = {}
+    for name, spec, res, hgt in [("cornell", scenes.cornell(), (32, 32, 32), 144),
+                                 ("atrium", scenes.atrium(detail=0.35), (64, 64, 64), 108),
+                                 ("terrain", scenes.terrain(120_000), (128, 128, 128), 90)]:
+        geo = rtc.Geometry(spec.positions, spec.tri_data, res)
+        out[name] = (spec, geo, rtc.Scene(geo, spec.materials, device=0), spec.camera(height=hgt))
+    yield out
+    for v in out.values():
+        v[2].close()
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.mark.parametrize("name", ["cornell", "atrium", "terrain"])
+def test_primary_hit_ids_bit_exact(orc, setups, name):
+    spec, geo, scene, cam = setups[name]
+    prm = rtc.make_params(mode=abi.RTC_MODE_PRIMARY)
+    g = scene.render(cam, prm, want_hits=True, want_radiance=True, want_stats=True)
+    o = orc.render(scene.desc, cam, prm, want_hits=True, want_radiance=True, want_stats=True)
+    assert np.array_equal(g["hit_id"], o["hit_id"])
+    assert (o["hit_id"] != abi.MISS_ID).mean() > 0.2          # the scene is actually in view
+    assert np.array_equal(_bits(g["hit_tuv"]), _bits(o["hit_tuv"]))
+    assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"]))
+    assert np.abs(g["rgb"].astype(int) - o["rgb"].astype(int)).max() <= 1
+    for k in ("rays", "cells_visited", "tris_tested", "hits_shaded", "paths"):
+        assert g["stats"][k] == o["stats"][k], k
+
+
+@pytest.mark.parametrize("name", ["cornell", "atrium"])
+def test_primary_matches_brute_force(orc, setups, name):
+    """cfg2: accelerated traversal vs a loop over ALL baked triangles (no grid), on a pixel subset."""
+    spec, geo, scene, cam = setups[name]
+    g = scene.render(cam, rtc.make_params(mode=abi.RTC_MODE_PRIMARY), want_hits=True)
+    rng = np.random.RandomState(0)
+    ties = 0
+    for _ in range(150 if name == "cornell" else 25):
+        x, y = rng.randint(cam.w), rng.randint(cam.h)
+        o, d = orc.camera_get_ray(cam, x + 0.5, y + 0.5)
+        idx, t, u, v = orc.trace_ray(scene.desc, o, d, brute=True)
+        want = abi.MISS_ID if idx < 0 else int(geo.tri_data["src_tri"][idx])
+        if want != int(g["hit_id"][y, x]):
+            ties += 1                                       # only an exact-t tie may differ (first tested wins)
+            assert g["hit_tuv"][y, x, 0] == np.float32(t)
+    assert ties <= 2
+
+
+@pytest.mark.parametrize("name,spp,bounce", [("cornell", 3, 4), ("cornell", 40, 6), ("atrium", 8, 4),
+                                             ("terrain", 5, 4), ("cornell", 33, 1), ("atrium", 2, 12)])
+def test_path_radiance_bit_exact(orc, setups, name, spp, bounce):
+    spec, geo, scene, cam = setups[name]
+    prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=0x1234567890 + spp)
+    g = scene.render(cam, prm, want_radiance=True, want_stats=True)
+    o = orc.render(scene.desc, cam, prm, want_radiance=True, want_stats=True)
+    assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"]))
+    assert np.abs(g["rgb"].astype(int) - o["rgb"].astype(int)).max() <= 1
+    assert (g["rgb"] != o["rgb"]).mean() < 0.02
+    for k in ("rays", "cells_visited", "tris_tested", "hits_shaded", "paths"):
+        assert g["stats"][k] == o["stats"][k], k
+    assert g["stats"]["paths"] == cam.w * cam.h * spp
+
+
+def test_fast_math_within_tolerance(orc, setups):
+    spec, geo, scene, cam = setups["atrium"]
+    o1 = orc.render(scene.desc, cam, rtc.make_params(mode=abi.RTC_MODE_PRIMARY), want_hits=True)
+    g1 = scene.render(cam, rtc.make_params(mode=abi.RTC_MODE_PRIMARY, math=abi.RTC_MATH_FAST), want_hits=True)
+    assert (g1["hit_id"] != o1["hit_id"]).mean() <= 1e-3        # stated near-tie fraction for the fast build
+    prm = rtc.make_params(num_samples=16, max_bounce=4, seed=9, math=abi.RTC_MATH_FAST)
+    g = scene.render(cam, prm, want_radiance=True)
+    o = orc.render(scene.desc, cam, rtc.make_params(num_samples=16, max_bounce=4, seed=9), want_radiance=True)
+    rmse = np.sqrt(np.mean((g["radiance"] - o["radiance"]) ** 2))
+    o2 = orc.render(scene.desc, cam, rtc.make_params(num_samples=16, max_bounce=4, seed=10), want_radiance=True)
+    noise = np.sqrt(np.mean((o2["radiance"] - o["radiance"]) ** 2))
+    assert rmse <= 0.05 * noise, (rmse, noise)                  # far below the Monte-Carlo noise floor
+
+
+def test_sample_sharding_and_row_sharding(orc, setups):
+    """§8(e): samples [0,S) split over two calls into one accumulator == one call, within fp32 sum
+    reordering; row bands from two 'ranks' tile the frame exactly."""
+    spec, geo, scene, cam = setups["cornell"]
+    full = scene.render(cam, rtc.make_params(num_samples=8, seed=3), want_radiance=True)
+    img = np.zeros((cam.h, cam.w, 3), np.uint8)
+    rad = []
+    for r in range(2):
+        out = scene.render(cam, rtc.make_params(num_samples=8, seed=3, tile_rank=r, tile_world=2), img=img, want_radiance=True)
+        rad.append(out["radiance"])
+    assert np.array_equal(img, full["rgb"])
+    h2 = cam.h // 2
+    assert np.array_equal(_bits(rad[0][:h2]), _bits(full["radiance"][:h2]))
+    assert np.array_equal(_bits(rad[1][h2:]), _bits(full["radiance"][h2:]))
+    import torch
+    acc = torch.zeros(cam.h * cam.w, 4, device="cuda:0")
+    for r in range(2):
+        scene.render_accumulate(cam, rtc.make_params(num_samples=4, seed=3, sample_offset=4 * r, total_samples=8), acc.data_ptr())
+    torch.cuda.synchronize()
+    d_rad = torch.zeros(cam.h * cam.w, 3, device="cuda:0")
+    d_rgb = torch.zeros(cam.h * cam.w, 3, dtype=torch.uint8, device="cuda:0")
+    rtc.resolve(acc.data_ptr(), cam.h * cam.w, 8, d_rgb.data_ptr(), d_rad.data_ptr(), device=0)
+    torch.cuda.synchronize()
+    assert float(acc[:, 3].min()) == 8.0 and float(acc[:, 3].max()) == 8.0
+    np.testing.assert_allclose(d_rad.cpu().numpy().reshape(cam.h, cam.w, 3), full["radiance"], rtol=2e-6, atol=1e-7)
+    assert np.abs(d_rgb.cpu().numpy().reshape(cam.h, cam.w, 3).astype(int) - full["rgb"].astype(int)).max() <= 1
+
+
+def test_edge_cases(orc):
+    """Empty scene, camera inside / outside / behind the grid, axis-parallel rays (±inf DDA lanes,
+    src/linalg.zig:609-651), single-cell grid, max_bounce = 0, and error codes."""
+    M = rtc.MaterialData
+    td0 = np.zeros(0, rtc.TRI_DATA_DTYPE)
+    # one emissive triangle facing +z, grid 1x1x1 and 5x5x5
+    pos = np.array([[[-1, -1, 0], [1, -1, 0], [0, 1, 0]]], np.float32)
+    td = np.zeros(1, rtc.TRI_DATA_DTYPE)
+    td["normal"][:] = (0, 0, 1)
+    mats = [M(base_color=(0.5, 0.5, 0.5), emissive=(2.0, 1.0, 0.5))]
+    cams = []
+    for eye, tgt in [((0, 0, 3), (0, 0, 0)), ((0, 0, 0.5), (0, 0, 0)), ((0, 0, -3), (0, 0, -6)), ((0, 0, -3), (0, 0, 0))]:
+        cams.append(scenes.load_camera(scenes.look_at(eye, tgt), 0.8, 1.0, None, 33))
+    axis = abi.Camera()                       # every ray exactly along -z (up/right of zero length in x,y jitter)
+    axis.w, axis.h = 8, 8
+    axis.origin[:] = (0.1, -0.2, 5.0); axis.lower_left_corner[:] = (0.0, 0.0, -1.0)
+    axis.right[:] = (0.0, 0.0, 0.0); axis.up[:] = (0.0, 0.0, 0.0)
+    cams.append(axis)
+    for res in [(1, 1, 1), (5, 5, 5), (3, 1, 7)]:
+        geo = rtc.Geometry(pos, td, res)
+        scene = rtc.Scene(geo, mats, device=0)
+        for cam in cams:
+            for prm in (rtc.make_params(mode=abi.RTC_MODE_PRIMARY), rtc.make_params(num_samples=5, max_bounce=3, seed=2),
+                        rtc.make_params(num_samples=2, max_bounce=0, seed=2)):
+                g = scene.render(cam, prm, want_radiance=True, want_hits=True)
+                o = orc.render(scene.desc, cam, prm, want_radiance=True, want_hits=True)
+                assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"]))
+                assert np.array_equal(g["hit_id"], o["hit_id"])
+        with pytest.raises(rtc.RtcError) as e:
+            scene.render(cams[0], rtc.make_params(num_samples=1, max_bounce=65))
+        assert e.value.code == abi.RTC_ERR_UNSUPPORTED
+        scene.close()
+    # empty scene: every pixel is sky
+    geo = rtc.Geometry(np.zeros((0, 3, 3), np.float32), td0, (4, 4, 4))
+    scene = rtc.Scene(geo, mats, device=0)
+    g = scene.render(cams[0], rtc.make_params(num_samples=4, seed=1), want_radiance=True, want_stats=True)
+    o = orc.render(scene.desc, cams[0], rtc.make_params(num_samples=4, seed=1), want_radiance=True)
+    assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"])) and g["stats"]["hits_shaded"] == 0
+    scene.close()

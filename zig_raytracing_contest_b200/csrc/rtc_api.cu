@@ -1,0 +1,448 @@
+// rtc_api.cu — the C ABI of include/rtc.h over the sm_100a kernels in rtc_kernels.cu.
+// Replaces `scene.render(threads, camera, img)` (src/main.zig:126, src/stage3.zig:247).
+// No CPU fallback: every compute entry point fails with RTC_ERR_NO_DEVICE without an sm_100 GPU.
+#include "../../include/rtc.h"
+#include "rtc_kernels.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+}  // namespace
+
+// used by rtc_geometry.cpp
+int rtc_set_error_(int code, const char* msg) { g_error = msg; return code; }
+
+namespace {
+
+#define CU(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(e_ == cudaErrorMemoryAllocation ? RTC_ERR_OUT_OF_MEMORY : RTC_ERR_CUDA,   \
+                        "%s: %s", #call, cudaGetErrorString(e_));                                 \
+    } while (0)
+
+float __uint_as_float_host(uint32_t u) { float f; memcpy(&f, &u, sizeof f); return f; }
+
+bool device_is_sm100(int dev)
+{
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return false;
+    return p.major == 10;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (dev != prev) cudaSetDevice(dev); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+// Device-resident scene + per-scene scratch reused across rtc_render calls.
+struct rtc_scene {
+    int device = 0;
+    int sm_count = 0;
+    rtc::DevScene dev{};
+    std::vector<void*> allocs;          // everything cudaMalloc'ed for the scene
+    unsigned long long* counters = nullptr;
+    uint32_t* work = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // frame scratch (grown on demand)
+    uint32_t cap_pixels = 0;
+    float4* accum = nullptr;
+    uint8_t* d_rgb = nullptr;
+    float* d_radiance = nullptr;
+    uint32_t* d_hit_id = nullptr;
+    float* d_hit_tuv = nullptr;
+    uint8_t* h_pinned = nullptr;        // staging for the D2H copies (rgb | radiance | hit_id | tuv)
+    size_t h_pinned_bytes = 0;
+    uint64_t num_tris = 0;
+    uint32_t num_src_tris = 0;
+
+    template <typename T>
+    int alloc(T** out, size_t count)
+    {
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, count ? count * sizeof(T) : sizeof(T));
+        if (e != cudaSuccess)
+            return fail(RTC_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes): %s", count * sizeof(T), cudaGetErrorString(e));
+        allocs.push_back(p);
+        *out = static_cast<T*>(p);
+        return RTC_OK;
+    }
+};
+
+extern "C" {
+
+const char* rtc_last_error(void) { return g_error.c_str(); }
+uint32_t rtc_abi_version(void) { return RTC_ABI_VERSION; }
+
+int rtc_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int ok = 0;
+    for (int i = 0; i < n; ++i) ok += device_is_sm100(i) ? 1 : 0;
+    return ok;
+}
+
+}  // extern "C"
+
+namespace {
+
+int upload_texture(rtc_scene* s, const rtc_texture& t, int want_channels, rtc::DevTexture* out,
+                   std::vector<std::pair<const float*, void*>>& seen)
+{
+    if (!t.texels || t.w <= 0 || t.h <= 0) return fail(RTC_ERR_INVALID_ARGUMENT, "texture without texels or with non-positive size");
+    if (t.channels != want_channels) return fail(RTC_ERR_INVALID_ARGUMENT, "texture has %d channels, expected %d", t.channels, want_channels);
+    if ((int64_t)t.w * t.h > (int64_t)1 << 30) return fail(RTC_ERR_UNSUPPORTED, "texture larger than 2^30 texels");
+    out->w = t.w; out->h = t.h;
+    out->u_min = t.u_min; out->u_max = t.u_max; out->v_min = t.v_min; out->v_max = t.v_max;
+    out->wf = (float)t.w; out->hf = (float)t.h;            // Texture.w/h: f32 (src/stage3.zig:85-86)
+    for (auto& kv : seen)
+        if (kv.first == t.texels) { out->texels = kv.second; return RTC_OK; }
+    const size_t n = (size_t)t.w * (size_t)t.h;
+    void* d = nullptr;
+    if (want_channels == 3) {
+        std::vector<float4> staged(n);
+        for (size_t i = 0; i < n; ++i) staged[i] = make_float4(t.texels[3 * i], t.texels[3 * i + 1], t.texels[3 * i + 2], 0.0f);
+        float4* dp = nullptr;
+        if (int rc = s->alloc(&dp, n)) return rc;
+        CU(cudaMemcpy(dp, staged.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+        d = dp;
+    } else {
+        float* dp = nullptr;
+        if (int rc = s->alloc(&dp, n)) return rc;
+        CU(cudaMemcpy(dp, t.texels, n * sizeof(float), cudaMemcpyHostToDevice));
+        d = dp;
+    }
+    seen.emplace_back(t.texels, d);
+    out->texels = d;
+    return RTC_OK;
+}
+
+int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
+{
+    const rtc_grid& g = desc->grid;
+    const uint64_t num_cells = (uint64_t)g.resolution[0] * g.resolution[1] * g.resolution[2];
+    if (g.resolution[0] == 0 || g.resolution[1] == 0 || g.resolution[2] == 0 || num_cells != desc->num_cells)
+        return fail(RTC_ERR_INVALID_ARGUMENT, "num_cells (%llu) does not match the grid resolution", (unsigned long long)desc->num_cells);
+    if (num_cells >= ((uint64_t)1 << 32) || desc->num_tris >= ((uint64_t)1 << 32))
+        return fail(RTC_ERR_UNSUPPORTED, "more than 2^32 cells or baked triangles");
+    if (!desc->cells || (desc->num_tris && (!desc->tri_pos || !desc->tri_data)) || !desc->materials || desc->num_materials == 0)
+        return fail(RTC_ERR_INVALID_ARGUMENT, "scene description has null arrays");
+
+    // validate cells + derive the occupancy bitmask
+    std::vector<uint32_t> occ((num_cells + 31) / 32, 0u);
+    for (uint64_t c = 0; c < num_cells; ++c) {
+        const rtc_cell& cell = desc->cells[c];
+        if (cell.begin > cell.end || cell.end > desc->num_tris)
+            return fail(RTC_ERR_INVALID_ARGUMENT, "cell %llu has range [%u,%u) outside the %llu baked triangles",
+                        (unsigned long long)c, cell.begin, cell.end, (unsigned long long)desc->num_tris);
+        if (cell.end > cell.begin) occ[c >> 5] |= 1u << (c & 31);
+    }
+    uint32_t num_src = desc->num_src_tris;
+    uint32_t max_src = 0;
+    for (uint64_t i = 0; i < desc->num_tris; ++i) {
+        if (desc->tri_data[i].material >= desc->num_materials)
+            return fail(RTC_ERR_INVALID_ARGUMENT, "baked triangle %llu references material %u of %u",
+                        (unsigned long long)i, desc->tri_data[i].material, desc->num_materials);
+        if (desc->tri_data[i].src_tri > max_src) max_src = desc->tri_data[i].src_tri;
+    }
+    if (num_src == 0) num_src = desc->num_tris ? max_src + 1 : 0;
+    if (desc->num_tris && max_src >= num_src) return fail(RTC_ERR_INVALID_ARGUMENT, "src_tri %u >= num_src_tris %u", max_src, num_src);
+
+    rtc::DevScene& d = s->dev;
+    for (int i = 0; i < 3; ++i) {
+        d.bmin[i] = g.bbox_min[i]; d.bmax[i] = g.bbox_max[i];
+        d.res[i] = g.resolution[i]; d.cell[i] = g.cell_size[i];
+    }
+    uint2* d_cells = nullptr; uint32_t* d_occ = nullptr; float4* d_pos = nullptr; float4* d_data = nullptr;
+    if (int rc = s->alloc(&d_cells, num_cells)) return rc;
+    if (int rc = s->alloc(&d_occ, occ.size())) return rc;
+    if (int rc = s->alloc(&d_pos, 3 * desc->num_tris)) return rc;
+    if (int rc = s->alloc(&d_data, 5 * (size_t)num_src)) return rc;
+    static_assert(sizeof(rtc_cell) == sizeof(uint2), "rtc_cell layout");
+    CU(cudaMemcpy(d_cells, desc->cells, num_cells * sizeof(uint2), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_occ, occ.data(), occ.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    {
+        // {v0,e1,e2} float4 rows; v0.w carries the source-triangle id (the reference's rows have an
+        // unused 4th lane: @Vector(3,f32) is 16 bytes), so a hit needs no extra index fetch.
+        std::vector<float4> pos(3 * desc->num_tris);
+        std::vector<float4> data(5 * (size_t)num_src, make_float4(0, 0, 0, 0));
+        for (uint64_t i = 0; i < desc->num_tris; ++i) {
+            const rtc_tri_pos& p = desc->tri_pos[i];
+            const rtc_tri_data& t = desc->tri_data[i];
+            pos[3 * i] = make_float4(p.v0[0], p.v0[1], p.v0[2], __uint_as_float_host(t.src_tri));
+            pos[3 * i + 1] = make_float4(p.e1[0], p.e1[1], p.e1[2], 0.0f);
+            pos[3 * i + 2] = make_float4(p.e2[0], p.e2[1], p.e2[2], 0.0f);
+            float w[20] = { 0 };
+            memcpy(w, t.normal, 9 * sizeof(float));
+            memcpy(w + 9, t.texcoord, 6 * sizeof(float));
+            memcpy(w + 15, &t.material, sizeof(uint32_t));
+            memcpy(w + 16, &t.src_tri, sizeof(uint32_t));
+            memcpy(&data[5 * (size_t)t.src_tri], w, sizeof w);
+        }
+        CU(cudaMemcpy(d_pos, pos.data(), pos.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(d_data, data.data(), data.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    }
+    std::vector<rtc::DevMaterial> mats(desc->num_materials);
+    std::vector<std::pair<const float*, void*>> seen;
+    for (uint32_t m = 0; m < desc->num_materials; ++m) {
+        if (int rc = upload_texture(s, desc->materials[m].base_color, 3, &mats[m].base, seen)) return rc;
+        if (int rc = upload_texture(s, desc->materials[m].emissive, 3, &mats[m].emissive, seen)) return rc;
+        if (int rc = upload_texture(s, desc->materials[m].transparency, 1, &mats[m].alpha, seen)) return rc;
+    }
+    rtc::DevMaterial* d_mats = nullptr;
+    if (int rc = s->alloc(&d_mats, mats.size())) return rc;
+    CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
+    d.cells = d_cells; d.occ = d_occ; d.tri_pos = d_pos; d.tri_data = d_data; d.materials = d_mats;
+    d.num_materials = desc->num_materials;
+    s->num_tris = desc->num_tris;
+    s->num_src_tris = num_src;
+
+    if (int rc = s->alloc(&s->counters, (size_t)rtc::CNT_N)) return rc;
+    if (int rc = s->alloc(&s->work, (size_t)4)) return rc;
+    CU(cudaMemset(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long)));
+    CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&s->ev0));
+    CU(cudaEventCreate(&s->ev1));
+    return RTC_OK;
+}
+
+void scene_free(rtc_scene* s)
+{
+    if (!s) return;
+    DeviceGuard guard(s->device);
+    cudaDeviceSynchronize();
+    for (void* p : s->allocs) cudaFree(p);
+    cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out)
+{
+    if (!desc || !out) return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_create: null argument");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return fail(RTC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)"); }
+    if (device < 0) CU(cudaGetDevice(&device));
+    if (device >= n) return fail(RTC_ERR_INVALID_ARGUMENT, "device %d of %d", device, n);
+    if (!device_is_sm100(device)) return fail(RTC_ERR_NO_DEVICE, "device %d is not sm_100 (kernels are built for sm_100a only)", device);
+    rtc_scene* s = new (std::nothrow) rtc_scene();
+    if (!s) return fail(RTC_ERR_OUT_OF_MEMORY, "host allocation failed");
+    s->device = device;
+    DeviceGuard guard(device);
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    s->sm_count = prop.multiProcessorCount;
+    const int rc = scene_upload(s, desc);
+    if (rc != RTC_OK) { const std::string keep = g_error; scene_free(s); g_error = keep; return rc; }
+    *out = s;
+    return RTC_OK;
+}
+
+void rtc_scene_destroy(rtc_scene* scene) { scene_free(scene); }
+
+}  // extern "C"
+
+namespace {
+
+rtc::DevCamera to_dev(const rtc_camera& c)
+{
+    rtc::DevCamera d;
+    d.w = c.w; d.h = c.h;
+    for (int i = 0; i < 3; ++i) { d.origin[i] = c.origin[i]; d.llc[i] = c.lower_left_corner[i]; d.right[i] = c.right[i]; d.up[i] = c.up[i]; }
+    return d;
+}
+
+int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_params* p)
+{
+    if (!s || !cam || !p) return fail(RTC_ERR_INVALID_ARGUMENT, "null scene, camera or params");
+    if (cam->w == 0 || cam->h == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "camera has zero size");
+    if ((uint64_t)cam->w * cam->h >= ((uint64_t)1 << 31)) return fail(RTC_ERR_UNSUPPORTED, "more than 2^31 pixels");
+    if (p->mode != RTC_MODE_PATH && p->mode != RTC_MODE_PRIMARY) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown mode %u", p->mode);
+    if (p->accel != RTC_ACCEL_GRID) return fail(RTC_ERR_UNSUPPORTED, "unknown accel %u", p->accel);
+    if (p->math != RTC_MATH_EXACT && p->math != RTC_MATH_FAST) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown math contract %u", p->math);
+    if (p->mode == RTC_MODE_PATH && p->max_bounce > 64)
+        return fail(RTC_ERR_UNSUPPORTED, "max_bounce %u > 64 (scatter stack capacity of the kernels)", (unsigned)p->max_bounce);
+    if (p->tile_world > 1 && p->tile_rank >= p->tile_world) return fail(RTC_ERR_INVALID_ARGUMENT, "tile_rank %u >= tile_world %u", p->tile_rank, p->tile_world);
+    return RTC_OK;
+}
+
+// Rows [y0,y1) of the frame that this call renders. Tile sharding = contiguous bands of rows:
+// rank r of n owns rows [r*h/n, (r+1)*h/n) (the reference's own split is contiguous pixel ranges
+// per worker, src/stage3.zig:228-233).
+void shard_rows(const rtc_camera* cam, const rtc_params* p, uint32_t* y0, uint32_t* y1)
+{
+    if (p->tile_world <= 1) { *y0 = 0; *y1 = cam->h; return; }
+    *y0 = (uint32_t)(((uint64_t)cam->h * p->tile_rank) / p->tile_world);
+    *y1 = (uint32_t)(((uint64_t)cam->h * (p->tile_rank + 1)) / p->tile_world);
+}
+
+int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, float4* accum,
+                  rtc::PrimaryOut pout, cudaStream_t stream)
+{
+    uint32_t y0, y1;
+    shard_rows(cam, p, &y0, &y1);
+    rtc::DevParams dp;
+    dp.num_samples = p->num_samples; dp.max_bounce = p->max_bounce; dp.sample_offset = p->sample_offset;
+    dp.seed_lo = (uint32_t)p->seed; dp.seed_hi = (uint32_t)(p->seed >> 32);
+    dp.first_pixel = y0 * cam->w; dp.num_pixels = (y1 - y0) * cam->w;
+    const rtc::DevCamera dc = to_dev(*cam);
+    rtc::LaunchCfg cfg; cfg.sm_count = s->sm_count; cfg.stream = stream; cfg.stats = p->collect_stats != 0;
+    cudaError_t e;
+    if (p->mode == RTC_MODE_PRIMARY)
+        e = p->math == RTC_MATH_FAST ? rtc::fast::launch_primary(s->dev, dc, dp, accum, pout, s->counters, cfg)
+                                     : rtc::exact::launch_primary(s->dev, dc, dp, accum, pout, s->counters, cfg);
+    else
+        e = p->math == RTC_MATH_FAST ? rtc::fast::launch_path(s->dev, dc, dp, accum, s->counters, s->work, cfg)
+                                     : rtc::exact::launch_path(s->dev, dc, dp, accum, s->counters, s->work, cfg);
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    return RTC_OK;
+}
+
+int ensure_frame(rtc_scene* s, uint32_t pixels)
+{
+    if (pixels <= s->cap_pixels) return RTC_OK;
+    cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    s->accum = nullptr; s->d_rgb = nullptr; s->d_radiance = nullptr; s->d_hit_id = nullptr; s->d_hit_tuv = nullptr;
+    s->h_pinned = nullptr; s->cap_pixels = 0;
+    CU(cudaMalloc(&s->accum, (size_t)pixels * sizeof(float4)));
+    CU(cudaMalloc(&s->d_rgb, (size_t)pixels * 3));
+    CU(cudaMalloc(&s->d_radiance, (size_t)pixels * 3 * sizeof(float)));
+    CU(cudaMalloc(&s->d_hit_id, (size_t)pixels * sizeof(uint32_t)));
+    CU(cudaMalloc(&s->d_hit_tuv, (size_t)pixels * 3 * sizeof(float)));
+    s->h_pinned_bytes = (size_t)pixels * (3 + 12 + 4 + 12);
+    CU(cudaMallocHost(&s->h_pinned, s->h_pinned_bytes));
+    s->cap_pixels = pixels;
+    return RTC_OK;
+}
+
+int read_counters(rtc_scene* s, rtc_stats* out)
+{
+    unsigned long long c[rtc::CNT_N];
+    CU(cudaMemcpy(c, s->counters, sizeof c, cudaMemcpyDeviceToHost));
+    CU(cudaMemset(s->counters, 0, sizeof c));
+    out->rays = c[rtc::CNT_RAYS]; out->cells_visited = c[rtc::CNT_CELLS]; out->tris_tested = c[rtc::CNT_TRIS];
+    out->hits_shaded = c[rtc::CNT_HITS]; out->paths = c[rtc::CNT_PATHS];
+    return RTC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t* rgb_out, rtc_aux* aux)
+{
+    if (int rc = check_render_args(s, cam, p)) return rc;
+    if (!rgb_out) return fail(RTC_ERR_INVALID_ARGUMENT, "rgb_out is null");
+    DeviceGuard guard(s->device);
+    const uint32_t pixels = cam->w * cam->h;
+    if (int rc = ensure_frame(s, pixels)) return rc;
+    const uint32_t total = p->mode == RTC_MODE_PRIMARY ? 1u : (p->total_samples ? p->total_samples : p->num_samples);
+    if (total == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "num_samples is zero");
+    uint32_t y0, y1;
+    shard_rows(cam, p, &y0, &y1);
+    const size_t first = (size_t)y0 * cam->w, count = (size_t)(y1 - y0) * cam->w;
+    const bool want_hits = p->mode == RTC_MODE_PRIMARY && aux && (aux->hit_id || aux->hit_tuv);
+    const bool want_rad = aux && aux->radiance;
+    cudaStream_t st = s->stream;
+    if (aux && aux->stats) CU(cudaMemsetAsync(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long), st));
+    CU(cudaMemsetAsync(s->accum + first, 0, count * sizeof(float4), st));
+    CU(cudaEventRecord(s->ev0, st));
+    rtc::PrimaryOut pout; pout.hit_id = want_hits ? s->d_hit_id : nullptr; pout.hit_tuv = want_hits ? s->d_hit_tuv : nullptr;
+    if (int rc = launch_render(s, cam, p, s->accum, pout, st)) return rc;
+    cudaError_t e = p->math == RTC_MATH_FAST
+        ? rtc::fast::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st)
+        : rtc::exact::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st);
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
+    CU(cudaEventRecord(s->ev1, st));
+    // D2H through the pinned staging buffer (rgb_out is pageable caller memory, src/main.zig:122).
+    uint8_t* h_rgb = s->h_pinned;
+    float* h_rad = (float*)(s->h_pinned + (size_t)pixels * 3);
+    uint32_t* h_id = (uint32_t*)(s->h_pinned + (size_t)pixels * 15);
+    float* h_tuv = (float*)(s->h_pinned + (size_t)pixels * 19);
+    CU(cudaMemcpyAsync(h_rgb, s->d_rgb + 3 * first, count * 3, cudaMemcpyDeviceToHost, st));
+    if (want_rad) CU(cudaMemcpyAsync(h_rad, s->d_radiance + 3 * first, count * 12, cudaMemcpyDeviceToHost, st));
+    if (want_hits && aux->hit_id) CU(cudaMemcpyAsync(h_id, s->d_hit_id + first, count * 4, cudaMemcpyDeviceToHost, st));
+    if (want_hits && aux->hit_tuv) CU(cudaMemcpyAsync(h_tuv, s->d_hit_tuv + 3 * first, count * 12, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    memcpy(rgb_out + 3 * first, h_rgb, count * 3);
+    if (want_rad) memcpy(aux->radiance + 3 * first, h_rad, count * 12);
+    if (want_hits && aux->hit_id) memcpy(aux->hit_id + first, h_id, count * 4);
+    if (want_hits && aux->hit_tuv) memcpy(aux->hit_tuv + 3 * first, h_tuv, count * 12);
+    if (aux && aux->stats) {
+        if (int rc = read_counters(s, aux->stats)) return rc;
+        float ms = 0.0f;
+        CU(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        aux->stats->kernel_ms = ms;
+    }
+    return RTC_OK;
+}
+
+int rtc_render_accumulate(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, void* d_accum, void* stream)
+{
+    if (int rc = check_render_args(s, cam, p)) return rc;
+    if (!d_accum) return fail(RTC_ERR_INVALID_ARGUMENT, "d_accum is null");
+    DeviceGuard guard(s->device);
+    rtc::PrimaryOut pout; pout.hit_id = nullptr; pout.hit_tuv = nullptr;
+    return launch_render(s, cam, p, (float4*)d_accum, pout, (cudaStream_t)stream);
+}
+
+int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples, void* d_rgb, void* d_radiance,
+                int device, void* stream)
+{
+    if (!d_accum || total_samples == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_resolve: null accumulator or zero samples");
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return fail(RTC_ERR_NO_DEVICE, "no CUDA device"); }
+    if (device < 0) CU(cudaGetDevice(&device));
+    DeviceGuard guard(device);
+    cudaError_t e = rtc::exact::launch_resolve((const float4*)d_accum, num_pixels, total_samples, (uint8_t*)d_rgb,
+                                               (float*)d_radiance, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
+    return RTC_OK;
+}
+
+int rtc_scene_stats(rtc_scene* s, rtc_stats* out)
+{
+    if (!s || !out) return fail(RTC_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard guard(s->device);
+    CU(cudaDeviceSynchronize());
+    memset(out, 0, sizeof *out);
+    return read_counters(s, out);
+}
+
+}  // extern "C"

@@ -1,0 +1,38 @@
+// rtc_kernels.h — launch entry points of the render kernels. rtc_kernels.cu is compiled twice,
+// once per arithmetic contract (namespace exact: -fmad=false; namespace fast: -fmad=true).
+#pragma once
+#include "rtc_device.cuh"
+
+namespace rtc {
+
+struct LaunchCfg {
+    int sm_count;          // SMs of the device the launch goes to
+    cudaStream_t stream;
+    bool stats;            // instrumented variant (cells/tris counters)
+};
+
+struct PrimaryOut {
+    uint32_t* hit_id;      // num_pixels, source-triangle id or 0xFFFFFFFF (may be null)
+    float* hit_tuv;        // 3*num_pixels (may be null)
+};
+
+#define RTC_DECLARE_LAUNCHERS(NS)                                                                     \
+    namespace NS {                                                                                    \
+    /* renderWorker + traceRayRecursive (src/stage3.zig:188-245): adds prm.num_samples samples of   */ \
+    /* every pixel in [first_pixel, first_pixel+num_pixels) into accum[pixel] (rgb sum, count).     */ \
+    cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParams& prm,           \
+                            float4* accum, unsigned long long* counters, uint32_t* work,              \
+                            const LaunchCfg& cfg);                                                    \
+    /* deterministic slice: centre ray, depth 1 (hit -> emissive, miss -> sky) + hit buffers.        */ \
+    cudaError_t launch_primary(const DevScene& sc, const DevCamera& cam, const DevParams& prm,        \
+                               float4* accum, PrimaryOut out, unsigned long long* counters,           \
+                               const LaunchCfg& cfg);                                                 \
+    /* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242).                                      */ \
+    cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,      \
+                               uint8_t* rgb, float* radiance, cudaStream_t stream);                   \
+    }
+
+RTC_DECLARE_LAUNCHERS(exact)
+RTC_DECLARE_LAUNCHERS(fast)
+
+}  // namespace rtc

@@ -1,0 +1,236 @@
+"""Host side of the render path: ctypes binding of librtc.so (include/rtc.h) and a Python mirror
+of the reference's call sequence around it:
+
+    geometry.build(); geometry.bakeInto(&scene)      src/main.zig:117-118  -> Geometry(...)
+    scene.render(threads, camera, img)               src/main.zig:126      -> Scene.render(camera, ...)
+
+There is no CPU fallback: a missing library raises at import of `lib()`, and every compute call
+fails with RTC_ERR_NO_DEVICE when no sm_100 GPU is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtc.so")
+_LIB = None
+
+TRI_DATA_DTYPE = np.dtype([("normal", "<f4", (3, 3)), ("texcoord", "<f4", (3, 2)),
+                           ("material", "<u4"), ("src_tri", "<u4")])
+
+
+class RtcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("rtc error %d: %s" % (code, message))
+        self.code = code
+
+
+def lib():
+    """Load librtc.so (built in-tree by csrc/Makefile / __graft_entry__.build())."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s is missing: run `make -C zig_raytracing_contest_b200/csrc` "
+                          "(there is no CPU fallback)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    L.rtc_last_error.restype = C.c_char_p
+    L.rtc_abi_version.restype = C.c_uint32
+    L.rtc_device_count.restype = C.c_int
+    L.rtc_scene_create.argtypes = [C.POINTER(abi.SceneDesc), C.c_int, C.POINTER(C.c_void_p)]
+    L.rtc_scene_destroy.argtypes = [C.c_void_p]
+    L.rtc_scene_destroy.restype = None
+    L.rtc_render.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Params), C.c_void_p,
+                             C.POINTER(abi.Aux)]
+    L.rtc_render_accumulate.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Params),
+                                        C.c_void_p, C.c_void_p]
+    L.rtc_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
+    L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
+    L.rtc_geometry_free.argtypes = [C.POINTER(abi.Geometry)]
+    L.rtc_geometry_free.restype = None
+    if L.rtc_abi_version() != abi.RTC_ABI_VERSION:
+        raise ImportError("librtc.so ABI %d != binding ABI %d" % (L.rtc_abi_version(), abi.RTC_ABI_VERSION))
+    _LIB = L
+    return L
+
+
+def _check(rc):
+    if rc != abi.RTC_OK:
+        raise RtcError(rc, lib().rtc_last_error().decode("utf-8", "replace"))
+
+
+def device_count():
+    return int(lib().rtc_device_count())
+
+
+# ---- stage2: Geometry.build + bakeInto ---------------------------------------------------------
+class Geometry:
+    """Uniform-grid build + bake of a triangle soup (src/stage2.zig:131-164) on the host threads.
+
+    positions: [N,3,3] world-space vertices; tri_data: N records of TRI_DATA_DTYPE (src_tri
+    ignored on input); resolution: config.json's grid_resolution.
+    """
+
+    def __init__(self, positions, tri_data, resolution):
+        positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 9)
+        tri_data = np.ascontiguousarray(tri_data, dtype=TRI_DATA_DTYPE)
+        if tri_data.shape[0] != positions.shape[0]:
+            raise ValueError("positions and tri_data disagree on the triangle count")
+        res = np.ascontiguousarray(resolution, dtype=np.uint32)
+        g = abi.Geometry()
+        _check(lib().rtc_geometry_build(positions.ctypes.data, tri_data.ctypes.data, positions.shape[0],
+                                        res.ctypes.data, C.byref(g)))
+        try:
+            nc, nt = int(g.num_cells), int(g.num_tris)
+            self.grid = abi.Grid.from_buffer_copy(g.grid)
+            self.cells = np.ctypeslib.as_array(C.cast(g.cells, C.POINTER(C.c_uint32)), (nc, 2)).copy()
+            if nt:
+                self.tri_pos = np.ctypeslib.as_array(C.cast(g.tri_pos, C.POINTER(C.c_float)), (nt, 3, 4)).copy()
+                raw = np.ctypeslib.as_array(C.cast(g.tri_data, C.POINTER(C.c_uint8)), (nt * 68,)).copy()
+                self.tri_data = raw.view(TRI_DATA_DTYPE)
+            else:
+                self.tri_pos = np.zeros((0, 3, 4), np.float32)
+                self.tri_data = np.zeros(0, TRI_DATA_DTYPE)
+            self.num_src_tris = int(g.num_src_tris)
+            self.empty_cells, self.min_tris, self.max_tris = int(g.empty_cells), int(g.min_tris), int(g.max_tris)
+        finally:
+            lib().rtc_geometry_free(C.byref(g))
+
+    @property
+    def num_tris(self):
+        return int(self.tri_pos.shape[0])
+
+
+# ---- materials -----------------------------------------------------------------------------------
+class TextureData:
+    """stage3.Texture(T) (src/stage3.zig:75-80): linear float texels + the clamp range that
+    stage1 derives from the sampler's wrap mode (src/stage1.zig:383-397)."""
+
+    def __init__(self, texels, clamp_u=False, clamp_v=False):
+        t = np.ascontiguousarray(texels, dtype=np.float32)
+        if t.ndim == 2:
+            t = t[:, :, None]
+        self.texels = t
+        self.h, self.w, self.channels = t.shape
+        i32 = np.iinfo(np.int32)
+        self.u_min, self.u_max = (0, self.w - 1) if clamp_u else (i32.min, i32.max)
+        self.v_min, self.v_max = (0, self.h - 1) if clamp_v else (i32.min, i32.max)
+
+    def as_struct(self):
+        return abi.Texture(self.texels.ctypes.data_as(C.POINTER(C.c_float)), self.w, self.h,
+                           self.u_min, self.u_max, self.v_min, self.v_max, self.channels)
+
+
+def constant_texture(value):
+    v = np.atleast_1d(np.asarray(value, dtype=np.float32))
+    return TextureData(v.reshape(1, 1, -1))
+
+
+class MaterialData:
+    """stage3.Material (src/stage3.zig:125-129)."""
+
+    def __init__(self, base_color=(0.8, 0.8, 0.8), emissive=(0.0, 0.0, 0.0), transparency=1.0):
+        def tex(x, ch):
+            if isinstance(x, TextureData):
+                return x
+            return constant_texture(x if ch == 3 else [x])
+        self.base_color, self.emissive, self.transparency = tex(base_color, 3), tex(emissive, 3), tex(transparency, 1)
+
+    def as_struct(self):
+        return abi.Material(self.base_color.as_struct(), self.emissive.as_struct(), self.transparency.as_struct())
+
+
+def make_scene_desc(geometry, materials):
+    """rtc_scene_desc over numpy-owned arrays. Returns (desc, keepalive)."""
+    mats = (abi.Material * len(materials))(*[m.as_struct() for m in materials])
+    desc = abi.SceneDesc()
+    desc.grid = geometry.grid
+    desc.cells = geometry.cells.ctypes.data_as(C.POINTER(abi.Cell))
+    desc.num_cells = geometry.cells.shape[0]
+    desc.tri_pos = geometry.tri_pos.ctypes.data_as(C.POINTER(abi.TriPos))
+    desc.tri_data = geometry.tri_data.ctypes.data_as(C.POINTER(abi.TriData))
+    desc.num_tris = geometry.tri_pos.shape[0]
+    desc.materials = mats
+    desc.num_materials = len(materials)
+    desc.num_src_tris = geometry.num_src_tris
+    return desc, (mats, geometry, materials)
+
+
+def make_params(num_samples=3, max_bounce=4, mode=abi.RTC_MODE_PATH, seed=0, sample_offset=0,
+                total_samples=0, math=abi.RTC_MATH_EXACT, tile_rank=0, tile_world=0, collect_stats=False):
+    """main.Config's num_samples / max_bounce (src/main.zig:56-61; config.json defaults 3 and 4)."""
+    p = abi.Params()
+    p.num_samples, p.max_bounce, p.mode, p.seed = num_samples, max_bounce, mode, seed
+    p.sample_offset, p.total_samples = sample_offset, total_samples
+    p.accel, p.math = abi.RTC_ACCEL_GRID, math
+    p.tile_rank, p.tile_world, p.collect_stats = tile_rank, tile_world, 1 if collect_stats else 0
+    return p
+
+
+# ---- stage3: Scene ---------------------------------------------------------------------------------
+class Scene:
+    """Device-resident stage3.Scene. `render` is the reference's Scene.render (src/stage3.zig:247)."""
+
+    def __init__(self, geometry, materials, device=-1):
+        self.desc, self._keep = make_scene_desc(geometry, materials)
+        self._h = C.c_void_p()
+        _check(lib().rtc_scene_create(C.byref(self.desc), device, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().rtc_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def render(self, camera, params, img=None, want_radiance=False, want_hits=False, want_stats=False):
+        """Blocking render into img ([h,w,3] uint8, row 0 = top). Returns a dict with rgb and the
+        optional aux outputs."""
+        w, h = int(camera.w), int(camera.h)
+        if img is None:
+            img = np.zeros((h, w, 3), np.uint8)
+        if img.shape != (h, w, 3) or img.dtype != np.uint8 or not img.flags.c_contiguous:
+            raise ValueError("img must be a contiguous [h,w,3] uint8 array")
+        out = {"rgb": img}
+        aux = abi.Aux()
+        if want_radiance:
+            out["radiance"] = np.zeros((h, w, 3), np.float32)
+            aux.radiance = out["radiance"].ctypes.data_as(C.POINTER(C.c_float))
+        if want_hits:
+            out["hit_id"] = np.full((h, w), abi.MISS_ID, np.uint32)
+            out["hit_tuv"] = np.zeros((h, w, 3), np.float32)
+            aux.hit_id = out["hit_id"].ctypes.data_as(C.POINTER(C.c_uint32))
+            aux.hit_tuv = out["hit_tuv"].ctypes.data_as(C.POINTER(C.c_float))
+        st = abi.Stats()
+        if want_stats:
+            aux.stats = C.pointer(st)
+        _check(lib().rtc_render(self._h, C.byref(camera), C.byref(params), img.ctypes.data, C.byref(aux)))
+        if want_stats:
+            out["stats"] = st.as_dict()
+        return out
+
+    def render_accumulate(self, camera, params, d_accum_ptr, stream_ptr=None):
+        """Adds params.num_samples samples per pixel into a device float4 accumulator (async)."""
+        _check(lib().rtc_render_accumulate(self._h, C.byref(camera), C.byref(params),
+                                           C.c_void_p(d_accum_ptr), C.c_void_p(stream_ptr or 0)))
+
+    def stats(self):
+        st = abi.Stats()
+        _check(lib().rtc_scene_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
+
+def resolve(d_accum_ptr, num_pixels, total_samples, d_rgb_ptr=None, d_radiance_ptr=None, device=-1, stream_ptr=None):
+    """pixel.mul(inv_num_samples).toRGB() on device buffers (src/stage3.zig:242)."""
+    _check(lib().rtc_resolve(C.c_void_p(d_accum_ptr), num_pixels, total_samples, C.c_void_p(d_rgb_ptr or 0),
+                             C.c_void_p(d_radiance_ptr or 0), device, C.c_void_p(stream_ptr or 0)))
+
+
+def bytes_per_frame(stats, num_pixels):
+    """algorithmic bytes at the reference's record sizes — 8 B per visited cell,
+    48 B per tested triangle, 224 B per shaded hit, 3 B per stored pixel."""
+    return 8 * stats["cells_visited"] + 48 * stats["tris_tested"] + 224 * stats["hits_shaded"] + 3 * num_pixels
