@@ -35,11 +35,14 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "cfg3_atrium_1080p_64spp"
 SEED = 1
+OVERRIDE = {}      # --spp / --height (profiling runs only; the default line uses the workload as named)
 
 
 def build_workload(name):
     from zig_raytracing_contest_b200 import rtc, scenes
     scene_name, kw, grid, height, spp, bounce = WORKLOADS[name]
+    spp = OVERRIDE.get("spp") or spp
+    height = OVERRIDE.get("height") or height
     spec = scenes.SCENES[scene_name](**kw)
     t0 = time.time()
     geo = rtc.Geometry(spec.positions, spec.tri_data, grid)
@@ -145,6 +148,8 @@ def run_reference(args, rank, world):
 
 
 def workload_config(name, spec, geo, cam, spp, bounce, world):
+    if OVERRIDE.get("spp") or OVERRIDE.get("height"):
+        name = "%s [override spp=%s height=%s]" % (name, OVERRIDE.get("spp") or "-", OVERRIDE.get("height") or "-")
     return {"workload": name, "scene": spec.name, "source_triangles": spec.num_tris, "baked_triangles": geo.num_tris,
             "grid": [int(x) for x in geo.grid.resolution], "width": int(cam.w), "height": int(cam.h),
             "spp_per_gpu": spp, "spp_total": spp * world, "max_bounce": bounce, "seed": SEED,
@@ -307,7 +312,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--cpu-rows", type=int, default=0, help="--impl reference: rows per step (0 = calibrate to ~8 s)")
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (profiling only)")
+    ap.add_argument("--height", type=int, default=0, help="override the workload's height (profiling only)")
     args = ap.parse_args()
+    OVERRIDE.update(spp=args.spp, height=args.height)
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

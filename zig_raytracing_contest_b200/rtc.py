@@ -208,6 +208,8 @@ class Scene:
         st = abi.Stats()
         if want_stats:
             aux.stats = C.pointer(st)
+            params = abi.Params.from_buffer_copy(params)
+            params.collect_stats = 1                 # instrumented kernels: cells / triangle-test counters
         _check(lib().rtc_render(self._h, C.byref(camera), C.byref(params), img.ctypes.data, C.byref(aux)))
         if want_stats:
             out["stats"] = st.as_dict()

@@ -289,6 +289,8 @@ def terrain(num_tris=5_000_000, seed=7):
                   transparency=T(checker(1024, 64, (1.0,), (0.0,)))))                                         # 7 MASK
     m = Mesh()
     n_sph, seg = 64, (48, 24)                       # 64 spheres x 48*24*2 = 147456 triangles
+    if num_tris < 1_000_000:
+        n_sph, seg = 16, (16, 8)                    # small test variants: 16 x 16*8*2 = 4096 triangles
     sph_tris = n_sph * seg[0] * seg[1] * 2
     nq = int(np.floor(np.sqrt((num_tris - sph_tris) / 2)))
     S = 200.0
