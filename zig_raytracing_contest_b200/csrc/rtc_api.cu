@@ -181,24 +181,25 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
         d.res[i] = g.resolution[i]; d.cell[i] = g.cell_size[i];
     }
     uint2* d_cells = nullptr; uint32_t* d_occ = nullptr; float4* d_pos = nullptr; float4* d_data = nullptr;
+    const size_t M = (size_t)desc->num_tris;
     if (int rc = s->alloc(&d_cells, num_cells)) return rc;
     if (int rc = s->alloc(&d_occ, occ.size())) return rc;
-    if (int rc = s->alloc(&d_pos, 3 * desc->num_tris)) return rc;
+    if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
     if (int rc = s->alloc(&d_data, 5 * (size_t)num_src)) return rc;
     static_assert(sizeof(rtc_cell) == sizeof(uint2), "rtc_cell layout");
     CU(cudaMemcpy(d_cells, desc->cells, num_cells * sizeof(uint2), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_occ, occ.data(), occ.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     {
-        // {v0,e1,e2} float4 rows; v0.w carries the source-triangle id (the reference's rows have an
-        // unused 4th lane: @Vector(3,f32) is 16 bytes), so a hit needs no extra index fetch.
-        std::vector<float4> pos(3 * desc->num_tris);
+        // SoA {v0}{e1}{e2} float4 arrays; v0.w carries the source-triangle id (the reference's rows have
+        // an unused 4th lane: @Vector(3,f32) is 16 bytes), so a hit needs no extra index fetch.
+        std::vector<float4> pos(3 * M);
         std::vector<float4> data(5 * (size_t)num_src, make_float4(0, 0, 0, 0));
-        for (uint64_t i = 0; i < desc->num_tris; ++i) {
+        for (size_t i = 0; i < M; ++i) {
             const rtc_tri_pos& p = desc->tri_pos[i];
             const rtc_tri_data& t = desc->tri_data[i];
-            pos[3 * i] = make_float4(p.v0[0], p.v0[1], p.v0[2], __uint_as_float_host(t.src_tri));
-            pos[3 * i + 1] = make_float4(p.e1[0], p.e1[1], p.e1[2], 0.0f);
-            pos[3 * i + 2] = make_float4(p.e2[0], p.e2[1], p.e2[2], 0.0f);
+            pos[i] = make_float4(p.v0[0], p.v0[1], p.v0[2], __uint_as_float_host(t.src_tri));
+            pos[M + i] = make_float4(p.e1[0], p.e1[1], p.e1[2], 0.0f);
+            pos[2 * M + i] = make_float4(p.e2[0], p.e2[1], p.e2[2], 0.0f);
             float w[20] = { 0 };
             memcpy(w, t.normal, 9 * sizeof(float));
             memcpy(w + 9, t.texcoord, 6 * sizeof(float));
@@ -219,7 +220,7 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;
     CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
-    d.cells = d_cells; d.occ = d_occ; d.tri_pos = d_pos; d.tri_data = d_data; d.materials = d_mats;
+    d.cells = d_cells; d.occ = d_occ; d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
     d.num_materials = desc->num_materials;
     s->num_tris = desc->num_tris;
     s->num_src_tris = num_src;

@@ -14,8 +14,9 @@ namespace rtc {
 
 // ---- device-side scene layout (HBM) ---------------------------------------------------
 // cells     : uint2[C]      {begin,end}                      8 B / cell, x fastest
-// tri_pos   : float4[3*M]   {v0,e1,e2}, w unused             48 B / baked triangle
-// tri_data  : float4[5*M]   n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat | src pad pad pad
+// tri_v0/e1/e2 : float4[M] each (SoA) {v0.xyz, src id bits} {e1.xyz,0} {e2.xyz,0}   48 B / baked triangle;
+//             SoA so that 32 lanes testing 32 consecutive triangles issue three fully coalesced LDG.128
+// tri_data  : float4[5*N]   per SOURCE triangle: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat | pad
 // texels    : float4[w*h] (rgb, pad) for base colour / emissive, float[w*h] for transparency
 // occ       : uint32[C/32]  bit c = cell c non-empty (skips the cells[] load for empty cells)
 struct DevTexture {
@@ -31,7 +32,9 @@ struct DevScene {
     uint32_t res[3];
     float cell[3];
     const uint2* cells;
-    const float4* tri_pos;
+    const float4* tri_v0;
+    const float4* tri_e1;
+    const float4* tri_e2;
     const float4* tri_data;
     const DevMaterial* materials;
     const uint32_t* occ;

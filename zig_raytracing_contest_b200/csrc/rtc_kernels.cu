@@ -1,12 +1,13 @@
 // rtc_kernels.cu — sm_100a render kernels for the reference's per-pixel path-tracing loop
 // (src/stage3.zig:152-245). Compiled twice: -DRTC_NS=exact -fmad=false and -DRTC_NS=fast -fmad=true.
 //
-// Mapping. One lane = one (pixel, sample) path. A warp takes a group of 32/min(S,32) consecutive
-// pixels from a persistent work counter, so the primary rays of a warp are coherent (same or
-// neighbouring pixels -> same cells, same triangle records, broadcast loads). Per-sample radiance
-// is staged in shared memory and summed by the pixel's first lane IN SAMPLE ORDER, which
-// reproduces renderWorker's sequential `pixel = pixel.add(ray_color)` (stage3.zig:237-241) bit
-// for bit in the exact build.
+// Mapping. One lane = one (pixel, sample) path; a warp takes a group of 32/min(S,32) consecutive
+// pixels from a persistent work counter. Scene.traceRay is WARP-COOPERATIVE (trace32 below): every
+// lane walks its own ray's DDA, but the triangle tests of all 32 rays are pooled and dealt out one
+// (ray, triangle) pair per lane, so the Möller–Trumbore loop — the reference's innermost loop —
+// runs with (nearly) full lanes whatever the per-cell triangle counts are, and 32 consecutive
+// triangles of a cell are fetched with three coalesced LDG.128 (SoA float4 arrays).
+// The per-lane version this replaced ran at 5.2 of 32 active lanes (profiles/r1a_*).
 #include "rtc_kernels.h"
 
 #ifndef RTC_NS
@@ -16,45 +17,141 @@
 namespace rtc {
 namespace RTC_NS {
 
-static constexpr int kThreads = 256;
+static constexpr int kThreads = 128;
 static constexpr int kWarps = kThreads / 32;
 static constexpr uint32_t kMiss = 0xFFFFFFFFu;
+static constexpr uint32_t kFull = 0xFFFFFFFFu;
+static constexpr int kMaxStep = 8;      // DDA steps a lane may take per round before the pooled triangle pass
 
 struct Hit { float t, u, v; uint32_t tri; };
-
 struct Counters { uint32_t rays, cells, tris, hits, paths; };
 
-// Scene.traceRay (src/stage3.zig:152-186): nearest hit over the grid cells along the ray, cells in
-// DDA order, triangles of a cell in baked order, strict `best.t > t && t > 0` (first tested wins).
-// occ[] only skips the cells[] load of empty cells; the DDA state advances exactly as in the
-// reference so every t_next_crossing is the reference's.
+// Per-warp staging for trace32.
+struct WarpShared {
+    float4 item[32][2];                 // compacted pending (ray, cell): {o.xyz, begin-excl bits} {d.xyz, owner lane bits}
+    unsigned long long best[32];        // per owner lane: min over (t bits << 32 | baked triangle index)
+    float col[32][3];                   // per-sample radiance for the in-order pixel sum
+};
+
+// Grid.Iterator (src/linalg.zig:471-497) in a register-lean form: instead of cell/exit/step per
+// axis it keeps the number of steps left to the exit cell and the linear-index stride per axis.
+// The t_next_crossing / t_delta arithmetic is the reference's, add for add.
+struct Trav {
+    float tx, ty, tz, dx, dy, dz;
+    uint32_t rx, ry, rz;                // steps left before cell[axis] == exit[axis]
+    uint32_t sx, sy, sz;                // wrapping linear-index strides: +-1, +-res.x, +-res.x*res.y
+    uint32_t ci;                        // Grid.linearlizeCellIdx(cell) (src/linalg.zig:429-431)
+};
+
+__device__ __forceinline__ bool trav_init(const DevScene& sc, const Ray& r, Trav& s)
+{
+    GridIter it;
+    if (!grid_trace_ray(sc, r, it)) return false;
+    const uint32_t rx = sc.res[0], rxy = sc.res[0] * sc.res[1];
+    s.tx = it.tx; s.ty = it.ty; s.tz = it.tz; s.dx = it.dx; s.dy = it.dy; s.dz = it.dz;
+    s.rx = it.sx == 1u ? it.ex - it.cx : it.cx;       // exit is res-1 when stepping up, 0 when stepping down
+    s.ry = it.sy == 1u ? it.ey - it.cy : it.cy;
+    s.rz = it.sz == 1u ? it.ez - it.cz : it.cz;
+    s.sx = it.sx; s.sy = it.sy * rx; s.sz = it.sz * rxy;
+    s.ci = it.cz * rxy + it.cy * rx + it.cx;
+    return true;
+}
+
+// Iterator.next: axis = {2,1,2,1,2,2,0,0}[(tx<ty)<<2 | (tx<tz)<<1 | (ty<tz)] (linalg.zig:479-484):
+// x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y).
+__device__ __forceinline__ float trav_next(Trav& s)
+{
+    const bool xy = s.tx < s.ty, xz = s.tx < s.tz, yz = s.ty < s.tz;
+    const bool ax = xy && xz, ay = !xy && yz;
+    const uint32_t left = ax ? s.rx : (ay ? s.ry : s.rz);
+    if (left == 0u) return __int_as_float(0x7f800000);
+    float t;
+    if (ax)      { t = s.tx; s.tx += s.dx; s.rx -= 1u; s.ci += s.sx; }
+    else if (ay) { t = s.ty; s.ty += s.dy; s.ry -= 1u; s.ci += s.sy; }
+    else         { t = s.tz; s.tz += s.dz; s.rz -= 1u; s.ci += s.sz; }
+    return t;
+}
+
+// Scene.traceRay (src/stage3.zig:152-186) for the 32 rays of a warp. Must be called by all 32 lanes
+// (inactive lanes pass active = false). Semantics per ray are the reference's: cells in DDA order;
+// within a cell the winner is the smallest (t, baked index) with t > 0, and it replaces the running
+// best only if strictly nearer — which is what the sequential `nearest.t > hit.t and hit.t > 0`
+// (stage3.zig:174) yields when triangles are tested in index order; the loop ends at the first cell
+// whose exit crossing is >= best.t (stage3.zig:179-182). occ[] only skips the cells[] load of empty
+// cells. u and v of the winner are recomputed once at the end with the same arithmetic.
 template <bool STATS>
-__device__ __forceinline__ Hit trace_ray(const DevScene& sc, const Ray& r, Counters& cn)
+__device__ __forceinline__ Hit trace32(const DevScene& sc, const Ray& r, bool active, WarpShared& ws, Counters& cn)
 {
     const float inf = __int_as_float(0x7f800000);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u, le_mask = lt_mask | (1u << lane);
     Hit best; best.t = inf; best.u = 0.0f; best.v = 0.0f; best.tri = kMiss;
-    cn.rays += 1;
-    GridIter it;
-    if (!grid_trace_ray(sc, r, it)) return best;
-    const uint32_t rx = sc.res[0], rxy = sc.res[0] * sc.res[1];
-    for (;;) {
-        const uint32_t ci = it.cz * rxy + it.cy * rx + it.cx;
-        if (STATS) cn.cells += 1;
-        if ((__ldg(sc.occ + (ci >> 5)) >> (ci & 31u)) & 1u) {
-            const uint2 c = __ldg(sc.cells + ci);
-            if (STATS) cn.tris += c.y - c.x;
-            for (uint32_t ti = c.x; ti < c.y; ++ti) {
-                const float4 a = __ldg(sc.tri_pos + 3u * (size_t)ti);
-                const float4 b = __ldg(sc.tri_pos + 3u * (size_t)ti + 1);
-                const float4 c2 = __ldg(sc.tri_pos + 3u * (size_t)ti + 2);
-                float t, u, v;
-                if (tri_ray(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c2.x, c2.y, c2.z), r, t, u, v)) {
-                    if (best.t > t && t > 0.0f) { best.t = t; best.u = u; best.v = v; best.tri = ti; }
+    Trav s;
+    bool alive = false;
+    if (active) { cn.rays += 1; alive = trav_init(sc, r, s); }
+    while (__ballot_sync(kFull, alive)) {
+        // ---- phase A: every live lane walks to its next non-empty cell (at most kMaxStep cells) ----
+        uint32_t begin = 0, cnt = 0;
+        if (alive) {
+#pragma unroll 1
+            for (int k = 0; k < kMaxStep; ++k) {
+                if (STATS) cn.cells += 1;
+                if ((__ldg(sc.occ + (s.ci >> 5)) >> (s.ci & 31u)) & 1u) {
+                    const uint2 c = __ldg(sc.cells + s.ci);
+                    begin = c.x; cnt = c.y - c.x;
+                    break;
                 }
+                const float tn = trav_next(s);
+                if (best.t <= tn) { alive = false; break; }
             }
         }
-        const float tn = grid_next(it);
-        if (best.t <= tn) break;
+        if (STATS) cn.tris += cnt;
+        const uint32_t pend = __ballot_sync(kFull, cnt != 0u);
+        if (pend == 0u) continue;
+        // ---- phase B: pooled (ray, triangle) pairs, one per lane per pass ----
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, d); if (lane >= (uint32_t)d) incl += v; }
+        const uint32_t excl = incl - cnt;
+        const uint32_t total = __shfl_sync(kFull, incl, 31);
+        if (cnt != 0u) {
+            const uint32_t rank = __popc(pend & lt_mask);
+            ws.item[rank][0] = make_float4(r.o.x, r.o.y, r.o.z, __uint_as_float(begin - excl));
+            ws.item[rank][1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(lane));
+            ws.best[lane] = ~0ull;
+        }
+        __syncwarp();
+        for (uint32_t base = 0; base < total; base += 32u) {
+            const bool mine = cnt != 0u && excl >= base && excl < base + 32u;
+            const uint32_t starts = __reduce_or_sync(kFull, mine ? 1u << (excl - base) : 0u);
+            const uint32_t before = __popc(__ballot_sync(kFull, cnt != 0u && excl < base));
+            const uint32_t j = base + lane;
+            if (j < total) {
+                const uint32_t rank = before + __popc(starts & le_mask) - 1u;
+                const float4 i0 = ws.item[rank][0], i1 = ws.item[rank][1];
+                const uint32_t ti = j + __float_as_uint(i0.w);
+                const float4 a = __ldg(sc.tri_v0 + ti), b = __ldg(sc.tri_e1 + ti), c = __ldg(sc.tri_e2 + ti);
+                Ray q; q.o = mk(i0.x, i0.y, i0.z); q.d = mk(i1.x, i1.y, i1.z);
+                float t, u, v;
+                if (tri_ray(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), q, t, u, v) && t > 0.0f)
+                    atomicMin(&ws.best[__float_as_uint(i1.w)], ((unsigned long long)__float_as_uint(t) << 32) | ti);
+            }
+        }
+        __syncwarp();
+        // ---- phase C: owners fold the cell's winner in and take the cell's exit crossing ----
+        if (cnt != 0u) {
+            const unsigned long long k = ws.best[lane];
+            const float t = __uint_as_float((uint32_t)(k >> 32));
+            if (k != ~0ull && best.t > t) { best.t = t; best.tri = (uint32_t)k; }
+            const float tn = trav_next(s);
+            if (best.t <= tn) alive = false;
+        }
+        __syncwarp();
+    }
+    if (best.tri != kMiss) {
+        const float4 a = __ldg(sc.tri_v0 + best.tri), b = __ldg(sc.tri_e1 + best.tri), c = __ldg(sc.tri_e2 + best.tri);
+        float t;
+        tri_ray(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), r, t, best.u, best.v);
     }
     return best;
 }
@@ -63,7 +160,7 @@ __device__ __forceinline__ Hit trace_ray(const DevScene& sc, const Ray& r, Count
 struct TriData { v3 n0, n1, n2; float uv0[2], uv1[2], uv2[2]; uint32_t material; };
 __device__ __forceinline__ uint32_t src_of(const DevScene& sc, uint32_t baked)
 {
-    return __float_as_uint(__ldg(&sc.tri_pos[3u * (size_t)baked].w));
+    return __float_as_uint(__ldg(&sc.tri_v0[baked].w));
 }
 __device__ __forceinline__ TriData load_tri_data(const DevScene& sc, uint32_t src)
 {
@@ -88,27 +185,31 @@ __device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, fl
     tv = d.uv0[1] * w + d.uv1[1] * u + d.uv2[1] * v;
 }
 
-// traceRayRecursive (src/stage3.zig:188-220) in iterative form. The reference returns
-// `emissive + albedo * recurse(...)` per scattering level; the exact build keeps the (emissive,
-// albedo) pair of every scattering level and unwinds innermost-first so the float evaluation
-// order is the recursion's. Alpha pass-through levels (stage3.zig:207-213) consume a depth level
-// and an RNG block but neither attenuate nor push.
+
+// traceRayRecursive (src/stage3.zig:188-220) for the 32 paths of a warp, in iterative form. The
+// reference returns `emissive + albedo * recurse(...)` per scattering level; the exact build keeps
+// the (emissive, albedo) pair of every scattering level and unwinds innermost-first so the float
+// evaluation order is the recursion's. Alpha pass-through levels (stage3.zig:207-213) consume a
+// depth level and an RNG block but neither attenuate nor push. The bounce loop is warp-uniform
+// (trace32 needs all lanes); finished lanes ride along inactive.
 template <bool STATS, int MAXB>
-__device__ __forceinline__ v3 trace_path(const DevScene& sc, const DevParams& prm, Ray ray,
-                                         uint32_t pixel, uint32_t sample, Counters& cn)
+__device__ __forceinline__ v3 trace_path32(const DevScene& sc, const DevParams& prm, Ray ray, bool on,
+                                           uint32_t pixel, uint32_t sample, WarpShared& ws, Counters& cn)
 {
-    const float inf = __int_as_float(0x7f800000);
-    const float eps = 1.1920928955078125e-07f;          // std.math.floatEps(f32)
 #ifdef RTC_MATH_FAST_BUILD
     v3 radiance = splat(0.0f), throughput = splat(1.0f);
 #else
     float st[MAXB][6];
     int top = 0;
 #endif
+    const float eps = 1.1920928955078125e-07f;          // std.math.floatEps(f32)
     v3 value = splat(0.0f);                              // depth == 0 -> zeroes (stage3.zig:189-191)
-    for (uint32_t depth = prm.max_bounce; depth > 0; --depth) {
-        const Hit hit = trace_ray<STATS>(sc, ray, cn);
-        if (hit.t == inf) { value = env_color(ray.d); break; }
+    uint32_t depth = prm.max_bounce;
+    on = on && depth > 0u;
+    while (__ballot_sync(kFull, on)) {
+        const Hit hit = trace32<STATS>(sc, ray, on, ws, cn);
+        if (!on) continue;
+        if (hit.tri == kMiss) { value = env_color(ray.d); on = false; continue; }
         cn.hits += 1;
         const TriData td = load_tri_data(sc, src_of(sc, hit.tri));
         const DevMaterial* m = sc.materials + td.material;
@@ -121,6 +222,8 @@ __device__ __forceinline__ v3 trace_path(const DevScene& sc, const DevParams& pr
         float rnd[4];
         rng_block(prm, pixel, sample, 1u + (prm.max_bounce - depth), rnd);
         ray.o = ray_at(ray, hit.t + eps);
+        depth -= 1u;
+        if (depth == 0u) on = false;
         if (rnd[0] > transparency) continue;             // same direction, no attenuation
         ray.d = normalize(normal + unit_vector(rnd[1], rnd[2]));
 #ifdef RTC_MATH_FAST_BUILD
@@ -150,7 +253,7 @@ __device__ __forceinline__ void flush_counters(const Counters& cn, unsigned long
     for (int i = 0; i < 5; ++i) {
         unsigned long long x = v[i];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(kFull, x, o);
         if ((threadIdx.x & 31) == 0 && x != 0 && (stats || (i != CNT_CELLS && i != CNT_TRIS)))
             atomicAdd(counters + i, x);
     }
@@ -162,8 +265,9 @@ k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera ca
        const __grid_constant__ DevParams prm, float4* __restrict__ accum,
        unsigned long long* __restrict__ counters, uint32_t* __restrict__ work)
 {
-    __shared__ float s_col[kWarps][32][3];
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    __shared__ WarpShared s_ws[kWarps];
+    const uint32_t lane = threadIdx.x & 31u;
+    WarpShared& ws = s_ws[threadIdx.x >> 5];
     const uint32_t S = prm.num_samples;
     const uint32_t SL = S < 32u ? S : 32u;              // lanes per pixel
     const uint32_t ppw = 32u / SL;                      // pixels per warp pass
@@ -174,7 +278,7 @@ k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera ca
     for (;;) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(work, 1u);
-        g = __shfl_sync(0xFFFFFFFFu, g, 0);
+        g = __shfl_sync(kFull, g, 0);
         if (g >= groups) break;
         const uint32_t local = g * ppw + pj;
         const bool lane_on = (pj < ppw) && (local < prm.num_pixels);
@@ -183,22 +287,23 @@ k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera ca
         v3 running = splat(0.0f);
         for (uint32_t pass = 0; pass < passes; ++pass) {
             const uint32_t s = pass * 32u + sj;
-            v3 col = splat(0.0f);
-            if (lane_on && s < S) {
-                const uint32_t sample = prm.sample_offset + s;
+            const bool on = lane_on && s < S;
+            const uint32_t sample = prm.sample_offset + s;
+            Ray ray; ray.o = splat(0.0f); ray.d = splat(0.0f);
+            if (on) {
                 float jit[4];
                 rng_block(prm, pixel, sample, 0u, jit);
-                const Ray ray = camera_ray(cam, x + jit[0], y + jit[1]);
+                ray = camera_ray(cam, x + jit[0], y + jit[1]);
                 cn.paths += 1;
-                col = trace_path<STATS, MAXB>(sc, prm, ray, pixel, sample, cn);
             }
-            s_col[warp][lane][0] = col.x; s_col[warp][lane][1] = col.y; s_col[warp][lane][2] = col.z;
+            const v3 col = trace_path32<STATS, MAXB>(sc, prm, ray, on, pixel, sample, ws, cn);
+            ws.col[lane][0] = col.x; ws.col[lane][1] = col.y; ws.col[lane][2] = col.z;
             __syncwarp();
-            if (lane_on && sj == 0) {
+            if (lane_on && sj == 0) {                    // pixel = pixel.add(ray_color), in sample order (stage3.zig:237-241)
                 const uint32_t left = S - pass * 32u;
                 const uint32_t n = left < SL ? left : SL;
                 for (uint32_t k = 0; k < n; ++k)
-                    running = running + mk(s_col[warp][lane + k][0], s_col[warp][lane + k][1], s_col[warp][lane + k][2]);
+                    running = running + mk(ws.col[lane + k][0], ws.col[lane + k][1], ws.col[lane + k][2]);
             }
             __syncwarp();
         }
@@ -220,18 +325,26 @@ k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera
           const __grid_constant__ DevParams prm, float4* __restrict__ accum, PrimaryOut out,
           unsigned long long* __restrict__ counters)
 {
-    const float inf = __int_as_float(0x7f800000);
+    __shared__ WarpShared s_ws[kWarps];
+    WarpShared& ws = s_ws[threadIdx.x >> 5];
     Counters cn = { 0, 0, 0, 0, 0 };
     const uint32_t stride = gridDim.x * kThreads;
-    for (uint32_t local = blockIdx.x * kThreads + threadIdx.x; local < prm.num_pixels; local += stride) {
+    const uint32_t rounds = (prm.num_pixels + stride - 1u) / stride;
+    for (uint32_t it = 0; it < rounds; ++it) {
+        const uint32_t local = it * stride + blockIdx.x * kThreads + threadIdx.x;
+        const bool on = local < prm.num_pixels;
         const uint32_t pixel = prm.first_pixel + local;
-        const float x = (float)(pixel % cam.w), y = (float)(pixel / cam.w);
-        const Ray ray = camera_ray(cam, x + 0.5f, y + 0.5f);
-        cn.paths += 1;
-        const Hit hit = trace_ray<STATS>(sc, ray, cn);
+        Ray ray; ray.o = splat(0.0f); ray.d = splat(0.0f);
+        if (on) {
+            const float x = (float)(pixel % cam.w), y = (float)(pixel / cam.w);
+            ray = camera_ray(cam, x + 0.5f, y + 0.5f);
+            cn.paths += 1;
+        }
+        const Hit hit = trace32<STATS>(sc, ray, on, ws, cn);
+        if (!on) continue;
         v3 col;
         uint32_t id = kMiss;
-        if (hit.t == inf) {
+        if (hit.tri == kMiss) {
             col = env_color(ray.d);
         } else {
             cn.hits += 1;
