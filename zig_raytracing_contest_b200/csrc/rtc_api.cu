@@ -155,14 +155,30 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     if (!desc->cells || (desc->num_tris && (!desc->tri_pos || !desc->tri_data)) || !desc->materials || desc->num_materials == 0)
         return fail(RTC_ERR_INVALID_ARGUMENT, "scene description has null arrays");
 
-    // validate cells + derive the occupancy bitmask
-    std::vector<uint32_t> occ((num_cells + 31) / 32, 0u);
-    for (uint64_t c = 0; c < num_cells; ++c) {
-        const rtc_cell& cell = desc->cells[c];
-        if (cell.begin > cell.end || cell.end > desc->num_tris)
-            return fail(RTC_ERR_INVALID_ARGUMENT, "cell %llu has range [%u,%u) outside the %llu baked triangles",
-                        (unsigned long long)c, cell.begin, cell.end, (unsigned long long)desc->num_tris);
-        if (cell.end > cell.begin) occ[c >> 5] |= 1u << (c & 31);
+    for (int a = 0; a < 3; ++a)
+        if (g.resolution[a] > rtc::kMaxGridRes)
+            return fail(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)",
+                        g.resolution[a], a, rtc::kMaxGridRes);
+    // validate cells; re-lay them out block-major (4x4x4-cell blocks) and derive the two occupancy levels
+    const uint32_t nbx = (g.resolution[0] + 3) / 4, nby = (g.resolution[1] + 3) / 4, nbz = (g.resolution[2] + 3) / 4;
+    const size_t nb = (size_t)nbx * nby * nbz;
+    std::vector<rtc_cell> cells_b(nb * 64, rtc_cell{ 0u, 0u });
+    std::vector<unsigned long long> fine(nb, 0ull);
+    std::vector<uint32_t> coarse((nb + 31) / 32, 0u);
+    {
+        uint64_t c = 0;
+        for (uint32_t z = 0; z < g.resolution[2]; ++z)
+            for (uint32_t y = 0; y < g.resolution[1]; ++y)
+                for (uint32_t x = 0; x < g.resolution[0]; ++x, ++c) {
+                    const rtc_cell& cell = desc->cells[c];
+                    if (cell.begin > cell.end || cell.end > desc->num_tris)
+                        return fail(RTC_ERR_INVALID_ARGUMENT, "cell %llu has range [%u,%u) outside the %llu baked triangles",
+                                    (unsigned long long)c, cell.begin, cell.end, (unsigned long long)desc->num_tris);
+                    const size_t bi = (x >> 2) + (size_t)nbx * ((y >> 2) + (size_t)nby * (z >> 2));
+                    const uint32_t b = (x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4);
+                    cells_b[bi * 64 + b] = cell;
+                    if (cell.end > cell.begin) { fine[bi] |= 1ull << b; coarse[bi >> 5] |= 1u << (bi & 31); }
+                }
     }
     uint32_t num_src = desc->num_src_tris;
     uint32_t max_src = 0;
@@ -180,15 +196,18 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
         d.bmin[i] = g.bbox_min[i]; d.bmax[i] = g.bbox_max[i];
         d.res[i] = g.resolution[i]; d.cell[i] = g.cell_size[i];
     }
-    uint2* d_cells = nullptr; uint32_t* d_occ = nullptr; float4* d_pos = nullptr; float4* d_data = nullptr;
+    uint2* d_cells = nullptr; unsigned long long* d_fine = nullptr; uint32_t* d_coarse = nullptr;
+    float4* d_pos = nullptr; float4* d_data = nullptr;
     const size_t M = (size_t)desc->num_tris;
-    if (int rc = s->alloc(&d_cells, num_cells)) return rc;
-    if (int rc = s->alloc(&d_occ, occ.size())) return rc;
+    if (int rc = s->alloc(&d_cells, cells_b.size())) return rc;
+    if (int rc = s->alloc(&d_fine, fine.size())) return rc;
+    if (int rc = s->alloc(&d_coarse, coarse.size())) return rc;
     if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
     if (int rc = s->alloc(&d_data, 5 * (size_t)num_src)) return rc;
     static_assert(sizeof(rtc_cell) == sizeof(uint2), "rtc_cell layout");
-    CU(cudaMemcpy(d_cells, desc->cells, num_cells * sizeof(uint2), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(d_occ, occ.data(), occ.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_cells, cells_b.data(), cells_b.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_fine, fine.data(), fine.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_coarse, coarse.data(), coarse.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     {
         // SoA {v0}{e1}{e2} float4 arrays; v0.w carries the source-triangle id (the reference's rows have
         // an unused 4th lane: @Vector(3,f32) is 16 bytes), so a hit needs no extra index fetch.
@@ -220,7 +239,8 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;
     CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
-    d.cells = d_cells; d.occ = d_occ; d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
+    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.nbx = nbx; d.nby = nby; d.coarse_words = (uint32_t)coarse.size();
+    d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
     d.num_materials = desc->num_materials;
     s->num_tris = desc->num_tris;
     s->num_src_tris = num_src;

@@ -13,12 +13,15 @@
 namespace rtc {
 
 // ---- device-side scene layout (HBM) ---------------------------------------------------
-// cells     : uint2[C]      {begin,end}                      8 B / cell, x fastest
+// cells     : uint2[64*NB]  {begin,end}, 8 B / cell, BLOCK-MAJOR: the grid is cut into 4x4x4-cell blocks
+//             (NB = ceil(rx/4)*ceil(ry/4)*ceil(rz/4), x fastest); record = block*64 + (x&3 | (y&3)<<2 | (z&3)<<4)
+// fine      : uint64[NB]    bit b = cell b of the block is non-empty. One 8-byte load covers every DDA step a
+//             ray takes inside the block (the per-step occupancy probe was the top stall of the first kernel)
+// coarse    : uint32[NB/32] bit = block has any triangle; 4 KiB at 128^3 -> staged in shared memory per CTA
 // tri_v0/e1/e2 : float4[M] each (SoA) {v0.xyz, src id bits} {e1.xyz,0} {e2.xyz,0}   48 B / baked triangle;
 //             SoA so that 32 lanes testing 32 consecutive triangles issue three fully coalesced LDG.128
 // tri_data  : float4[5*N]   per SOURCE triangle: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat | pad
 // texels    : float4[w*h] (rgb, pad) for base colour / emissive, float[w*h] for transparency
-// occ       : uint32[C/32]  bit c = cell c non-empty (skips the cells[] load for empty cells)
 struct DevTexture {
     const void* texels;
     int w, h, u_min, u_max, v_min, v_max;
@@ -37,9 +40,14 @@ struct DevScene {
     const float4* tri_e2;
     const float4* tri_data;
     const DevMaterial* materials;
-    const uint32_t* occ;
+    const unsigned long long* fine;
+    const uint32_t* coarse;
+    uint32_t nbx, nby;          // blocks along x and y
+    uint32_t coarse_words;
     uint32_t num_materials;
 };
+static constexpr uint32_t kMaxGridRes = 1024;     // cell coordinates travel packed, 10 bits per axis
+static constexpr uint32_t kCoarseSmemMaxWords = 8192;   // 32 KiB: the coarse bitmap of a 256^3 grid
 struct DevCamera {
     uint32_t w, h;
     float origin[3], llc[3], right[3], up[3];

@@ -33,42 +33,61 @@ struct WarpShared {
     float col[32][3];                   // per-sample radiance for the in-order pixel sum
 };
 
-// Grid.Iterator (src/linalg.zig:471-497) in a register-lean form: instead of cell/exit/step per
-// axis it keeps the number of steps left to the exit cell and the linear-index stride per axis.
-// The t_next_crossing / t_delta arithmetic is the reference's, add for add.
+// Grid.Iterator (src/linalg.zig:471-497) in a register-lean, branch-free form. The cell travels packed
+// (x | y<<10 | z<<20) next to the packed exit cell; t_delta carries the step direction in its sign bit.
+// The t_next_crossing / t_delta arithmetic is the reference's, add for add. `fine` is the occupancy mask
+// of the 4x4x4 block the cell lies in, `bi` that block's index (rtc_device.cuh).
 struct Trav {
-    float tx, ty, tz, dx, dy, dz;
-    uint32_t rx, ry, rz;                // steps left before cell[axis] == exit[axis]
-    uint32_t sx, sy, sz;                // wrapping linear-index strides: +-1, +-res.x, +-res.x*res.y
-    uint32_t ci;                        // Grid.linearlizeCellIdx(cell) (src/linalg.zig:429-431)
+    float tx, ty, tz;                   // t_next_crossing
+    float dx, dy, dz;                   // |.| = t_delta; sign bit set = stepping towards 0 on that axis
+    uint32_t c, ec;                     // packed cell, packed exit cell
+    uint32_t bi;
+    unsigned long long fine;
 };
 
-__device__ __forceinline__ bool trav_init(const DevScene& sc, const Ray& r, Trav& s)
+static constexpr uint32_t kBlockBits = 0x3FCFF3FCu;    // bits 2..9 of each 10-bit field: the block coordinates
+
+template <bool CSM>
+__device__ __forceinline__ void trav_load_block(const DevScene& sc, const uint32_t* __restrict__ coarse, Trav& s)
+{
+    const uint32_t bx = (s.c >> 2) & 0xFFu, by = (s.c >> 12) & 0xFFu, bz = (s.c >> 22) & 0xFFu;
+    s.bi = bx + sc.nbx * (by + sc.nby * bz);
+    const uint32_t w = CSM ? coarse[s.bi >> 5] : __ldg(sc.coarse + (s.bi >> 5));
+    s.fine = ((w >> (s.bi & 31u)) & 1u) ? __ldg(sc.fine + s.bi) : 0ull;
+}
+// bit of the cell inside its block: x&3 | (y&3)<<2 | (z&3)<<4
+__device__ __forceinline__ uint32_t trav_cell_bit(uint32_t c) { return (c & 3u) | ((c >> 8) & 0xCu) | ((c >> 16) & 0x30u); }
+
+template <bool CSM>
+__device__ __forceinline__ bool trav_init(const DevScene& sc, const uint32_t* __restrict__ coarse, const Ray& r, Trav& s)
 {
     GridIter it;
     if (!grid_trace_ray(sc, r, it)) return false;
-    const uint32_t rx = sc.res[0], rxy = sc.res[0] * sc.res[1];
-    s.tx = it.tx; s.ty = it.ty; s.tz = it.tz; s.dx = it.dx; s.dy = it.dy; s.dz = it.dz;
-    s.rx = it.sx == 1u ? it.ex - it.cx : it.cx;       // exit is res-1 when stepping up, 0 when stepping down
-    s.ry = it.sy == 1u ? it.ey - it.cy : it.cy;
-    s.rz = it.sz == 1u ? it.ez - it.cz : it.cz;
-    s.sx = it.sx; s.sy = it.sy * rx; s.sz = it.sz * rxy;
-    s.ci = it.cz * rxy + it.cy * rx + it.cx;
+    s.tx = it.tx; s.ty = it.ty; s.tz = it.tz;
+    s.dx = __uint_as_float(__float_as_uint(it.dx) | (it.sx == 1u ? 0u : 0x80000000u));
+    s.dy = __uint_as_float(__float_as_uint(it.dy) | (it.sy == 1u ? 0u : 0x80000000u));
+    s.dz = __uint_as_float(__float_as_uint(it.dz) | (it.sz == 1u ? 0u : 0x80000000u));
+    s.c = it.cx | (it.cy << 10) | (it.cz << 20);
+    s.ec = it.ex | (it.ey << 10) | (it.ez << 20);
+    trav_load_block<CSM>(sc, coarse, s);
     return true;
 }
 
 // Iterator.next: axis = {2,1,2,1,2,2,0,0}[(tx<ty)<<2 | (tx<tz)<<1 | (ty<tz)] (linalg.zig:479-484):
-// x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y).
+// x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y). Returns +inf without
+// moving when the cell is the exit cell on that axis (linalg.zig:486-488).
 __device__ __forceinline__ float trav_next(Trav& s)
 {
     const bool xy = s.tx < s.ty, xz = s.tx < s.tz, yz = s.ty < s.tz;
-    const bool ax = xy && xz, ay = !xy && yz;
-    const uint32_t left = ax ? s.rx : (ay ? s.ry : s.rz);
-    if (left == 0u) return __int_as_float(0x7f800000);
-    float t;
-    if (ax)      { t = s.tx; s.tx += s.dx; s.rx -= 1u; s.ci += s.sx; }
-    else if (ay) { t = s.ty; s.ty += s.dy; s.ry -= 1u; s.ci += s.sy; }
-    else         { t = s.tz; s.tz += s.dz; s.rz -= 1u; s.ci += s.sz; }
+    const bool ax = xy && xz, ay = !xy && yz, az = !ax && !ay;
+    const float t = ax ? s.tx : (ay ? s.ty : s.tz);
+    const float d = ax ? s.dx : (ay ? s.dy : s.dz);
+    const uint32_t m = ax ? 0x3FFu : (ay ? 0xFFC00u : 0x3FF00000u);
+    if (((s.c ^ s.ec) & m) == 0u) return __int_as_float(0x7f800000);
+    const uint32_t one = m & 0x00100401u;
+    s.c = (__float_as_uint(d) >> 31) ? s.c - one : s.c + one;
+    const float tn = t + fabsf(d);
+    s.tx = ax ? tn : s.tx; s.ty = ay ? tn : s.ty; s.tz = az ? tn : s.tz;
     return t;
 }
 
@@ -77,10 +96,11 @@ __device__ __forceinline__ float trav_next(Trav& s)
 // within a cell the winner is the smallest (t, baked index) with t > 0, and it replaces the running
 // best only if strictly nearer — which is what the sequential `nearest.t > hit.t and hit.t > 0`
 // (stage3.zig:174) yields when triangles are tested in index order; the loop ends at the first cell
-// whose exit crossing is >= best.t (stage3.zig:179-182). occ[] only skips the cells[] load of empty
-// cells. u and v of the winner are recomputed once at the end with the same arithmetic.
-template <bool STATS>
-__device__ __forceinline__ Hit trace32(const DevScene& sc, const Ray& r, bool active, WarpShared& ws, Counters& cn)
+// whose exit crossing is >= best.t (stage3.zig:179-182). The block occupancy masks only skip the cells[] load
+// of empty cells. u and v of the winner are recomputed once at the end with the same arithmetic.
+template <bool STATS, bool CSM>
+__device__ __forceinline__ Hit trace32(const DevScene& sc, const uint32_t* __restrict__ coarse, const Ray& r, bool active,
+                                       WarpShared& ws, Counters& cn)
 {
     const float inf = __int_as_float(0x7f800000);
     const uint32_t lane = threadIdx.x & 31u;
@@ -88,7 +108,7 @@ __device__ __forceinline__ Hit trace32(const DevScene& sc, const Ray& r, bool ac
     Hit best; best.t = inf; best.u = 0.0f; best.v = 0.0f; best.tri = kMiss;
     Trav s;
     bool alive = false;
-    if (active) { cn.rays += 1; alive = trav_init(sc, r, s); }
+    if (active) { cn.rays += 1; alive = trav_init<CSM>(sc, coarse, r, s); }
     while (__ballot_sync(kFull, alive)) {
         // ---- phase A: every live lane walks to its next non-empty cell (at most kMaxStep cells) ----
         uint32_t begin = 0, cnt = 0;
@@ -96,13 +116,16 @@ __device__ __forceinline__ Hit trace32(const DevScene& sc, const Ray& r, bool ac
 #pragma unroll 1
             for (int k = 0; k < kMaxStep; ++k) {
                 if (STATS) cn.cells += 1;
-                if ((__ldg(sc.occ + (s.ci >> 5)) >> (s.ci & 31u)) & 1u) {
-                    const uint2 c = __ldg(sc.cells + s.ci);
+                const uint32_t b = trav_cell_bit(s.c);
+                if ((uint32_t)(s.fine >> b) & 1u) {
+                    const uint2 c = __ldg(sc.cells + (s.bi * 64u + b));
                     begin = c.x; cnt = c.y - c.x;
                     break;
                 }
+                const uint32_t c0 = s.c;
                 const float tn = trav_next(s);
                 if (best.t <= tn) { alive = false; break; }
+                if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
             }
         }
         if (STATS) cn.tris += cnt;
@@ -143,8 +166,10 @@ __device__ __forceinline__ Hit trace32(const DevScene& sc, const Ray& r, bool ac
             const unsigned long long k = ws.best[lane];
             const float t = __uint_as_float((uint32_t)(k >> 32));
             if (k != ~0ull && best.t > t) { best.t = t; best.tri = (uint32_t)k; }
+            const uint32_t c0 = s.c;
             const float tn = trav_next(s);
             if (best.t <= tn) alive = false;
+            else if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
         }
         __syncwarp();
     }
@@ -192,9 +217,9 @@ __device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, fl
 // evaluation order is the recursion's. Alpha pass-through levels (stage3.zig:207-213) consume a
 // depth level and an RNG block but neither attenuate nor push. The bounce loop is warp-uniform
 // (trace32 needs all lanes); finished lanes ride along inactive.
-template <bool STATS, int MAXB>
-__device__ __forceinline__ v3 trace_path32(const DevScene& sc, const DevParams& prm, Ray ray, bool on,
-                                           uint32_t pixel, uint32_t sample, WarpShared& ws, Counters& cn)
+template <bool STATS, int MAXB, bool CSM>
+__device__ __forceinline__ v3 trace_path32(const DevScene& sc, const uint32_t* __restrict__ coarse, const DevParams& prm, Ray ray,
+                                           bool on, uint32_t pixel, uint32_t sample, WarpShared& ws, Counters& cn)
 {
 #ifdef RTC_MATH_FAST_BUILD
     v3 radiance = splat(0.0f), throughput = splat(1.0f);
@@ -207,7 +232,7 @@ __device__ __forceinline__ v3 trace_path32(const DevScene& sc, const DevParams& 
     uint32_t depth = prm.max_bounce;
     on = on && depth > 0u;
     while (__ballot_sync(kFull, on)) {
-        const Hit hit = trace32<STATS>(sc, ray, on, ws, cn);
+        const Hit hit = trace32<STATS, CSM>(sc, coarse, ray, on, ws, cn);
         if (!on) continue;
         if (hit.tri == kMiss) { value = env_color(ray.d); on = false; continue; }
         cn.hits += 1;
@@ -259,13 +284,26 @@ __device__ __forceinline__ void flush_counters(const Counters& cn, unsigned long
     }
 }
 
-template <bool STATS, int MAXB>
+// The coarse block bitmap staged in (dynamic) shared memory once per CTA; nullptr when it does not fit
+// (CSM = false: probed in global memory instead).
+template <bool CSM>
+__device__ __forceinline__ const uint32_t* stage_coarse(const DevScene& sc)
+{
+    extern __shared__ uint32_t s_coarse[];
+    if (!CSM) return nullptr;
+    for (uint32_t i = threadIdx.x; i < sc.coarse_words; i += kThreads) s_coarse[i] = __ldg(sc.coarse + i);
+    __syncthreads();
+    return s_coarse;
+}
+
+template <bool STATS, int MAXB, bool CSM>
 __global__ void __launch_bounds__(kThreads)
 k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam,
        const __grid_constant__ DevParams prm, float4* __restrict__ accum,
        unsigned long long* __restrict__ counters, uint32_t* __restrict__ work)
 {
     __shared__ WarpShared s_ws[kWarps];
+    const uint32_t* coarse = stage_coarse<CSM>(sc);
     const uint32_t lane = threadIdx.x & 31u;
     WarpShared& ws = s_ws[threadIdx.x >> 5];
     const uint32_t S = prm.num_samples;
@@ -296,7 +334,7 @@ k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera ca
                 ray = camera_ray(cam, x + jit[0], y + jit[1]);
                 cn.paths += 1;
             }
-            const v3 col = trace_path32<STATS, MAXB>(sc, prm, ray, on, pixel, sample, ws, cn);
+            const v3 col = trace_path32<STATS, MAXB, CSM>(sc, coarse, prm, ray, on, pixel, sample, ws, cn);
             ws.col[lane][0] = col.x; ws.col[lane][1] = col.y; ws.col[lane][2] = col.z;
             __syncwarp();
             if (lane_on && sj == 0) {                    // pixel = pixel.add(ray_color), in sample order (stage3.zig:237-241)
@@ -319,13 +357,14 @@ k_path(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera ca
 // Deterministic slice (RTC_MODE_PRIMARY): Camera.getRay at the pixel centre + Scene.traceRay, then
 // traceRayRecursive with depth 1 and no RNG: hit -> emissive sample, miss -> sky. One lane per
 // pixel; a warp covers 32 consecutive pixels of a row.
-template <bool STATS>
+template <bool STATS, bool CSM>
 __global__ void __launch_bounds__(kThreads)
 k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam,
           const __grid_constant__ DevParams prm, float4* __restrict__ accum, PrimaryOut out,
           unsigned long long* __restrict__ counters)
 {
     __shared__ WarpShared s_ws[kWarps];
+    const uint32_t* coarse = stage_coarse<CSM>(sc);
     WarpShared& ws = s_ws[threadIdx.x >> 5];
     Counters cn = { 0, 0, 0, 0, 0 };
     const uint32_t stride = gridDim.x * kThreads;
@@ -340,7 +379,7 @@ k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera
             ray = camera_ray(cam, x + 0.5f, y + 0.5f);
             cn.paths += 1;
         }
-        const Hit hit = trace32<STATS>(sc, ray, on, ws, cn);
+        const Hit hit = trace32<STATS, CSM>(sc, coarse, ray, on, ws, cn);
         if (!on) continue;
         v3 col;
         uint32_t id = kMiss;
@@ -387,23 +426,34 @@ k_resolve(const float4* __restrict__ accum, uint32_t num_pixels, uint32_t total_
 }
 
 template <typename K>
-static int blocks_per_sm(K kernel)
+static int blocks_per_sm(K kernel, size_t smem)
 {
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, smem) != cudaSuccess || n < 1) n = 1;
     return n;
 }
 
-template <bool STATS, int MAXB>
+static bool coarse_in_smem(const DevScene& sc) { return sc.coarse_words <= kCoarseSmemMaxWords; }
+
+template <bool STATS, int MAXB, bool CSM>
 static cudaError_t run_path(const DevScene& sc, const DevCamera& cam, const DevParams& prm, float4* accum,
                             unsigned long long* counters, uint32_t* work, const LaunchCfg& cfg)
 {
-    auto kern = k_path<STATS, MAXB>;
-    const int grid = cfg.sm_count * blocks_per_sm(kern);   // persistent: one wave, dynamic work counter
+    auto kern = k_path<STATS, MAXB, CSM>;
+    const size_t smem = CSM ? sc.coarse_words * sizeof(uint32_t) : 0;
+    const int grid = cfg.sm_count * blocks_per_sm(kern, smem);   // persistent: one wave, dynamic work counter
     cudaError_t e = cudaMemsetAsync(work, 0, sizeof(uint32_t), cfg.stream);
     if (e != cudaSuccess) return e;
-    kern<<<grid, kThreads, 0, cfg.stream>>>(sc, cam, prm, accum, counters, work);
+    kern<<<grid, kThreads, smem, cfg.stream>>>(sc, cam, prm, accum, counters, work);
     return cudaGetLastError();
+}
+
+template <bool STATS, int MAXB>
+static cudaError_t run_path_csm(const DevScene& sc, const DevCamera& cam, const DevParams& prm, float4* accum,
+                                unsigned long long* counters, uint32_t* work, const LaunchCfg& cfg)
+{
+    return coarse_in_smem(sc) ? run_path<STATS, MAXB, true>(sc, cam, prm, accum, counters, work, cfg)
+                              : run_path<STATS, MAXB, false>(sc, cam, prm, accum, counters, work, cfg);
 }
 
 cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParams& prm, float4* accum,
@@ -411,27 +461,35 @@ cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParam
 {
     if (prm.num_pixels == 0 || prm.num_samples == 0) return cudaSuccess;
     if (prm.max_bounce <= 8)
-        return cfg.stats ? run_path<true, 8>(sc, cam, prm, accum, counters, work, cfg)
-                         : run_path<false, 8>(sc, cam, prm, accum, counters, work, cfg);
+        return cfg.stats ? run_path_csm<true, 8>(sc, cam, prm, accum, counters, work, cfg)
+                         : run_path_csm<false, 8>(sc, cam, prm, accum, counters, work, cfg);
     if (prm.max_bounce <= 64)
-        return cfg.stats ? run_path<true, 64>(sc, cam, prm, accum, counters, work, cfg)
-                         : run_path<false, 64>(sc, cam, prm, accum, counters, work, cfg);
+        return cfg.stats ? run_path_csm<true, 64>(sc, cam, prm, accum, counters, work, cfg)
+                         : run_path_csm<false, 64>(sc, cam, prm, accum, counters, work, cfg);
     return cudaErrorInvalidValue;
+}
+
+template <bool STATS, bool CSM>
+static cudaError_t run_primary(const DevScene& sc, const DevCamera& cam, const DevParams& prm, float4* accum,
+                               PrimaryOut out, unsigned long long* counters, const LaunchCfg& cfg)
+{
+    auto kern = k_primary<STATS, CSM>;
+    const size_t smem = CSM ? sc.coarse_words * sizeof(uint32_t) : 0;
+    const uint32_t need = (prm.num_pixels + kThreads - 1) / kThreads;
+    const uint32_t cap = (uint32_t)(cfg.sm_count * blocks_per_sm(kern, smem));
+    kern<<<need < cap ? need : cap, kThreads, smem, cfg.stream>>>(sc, cam, prm, accum, out, counters);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_primary(const DevScene& sc, const DevCamera& cam, const DevParams& prm, float4* accum,
                            PrimaryOut out, unsigned long long* counters, const LaunchCfg& cfg)
 {
     if (prm.num_pixels == 0) return cudaSuccess;
-    const uint32_t need = (prm.num_pixels + kThreads - 1) / kThreads;
-    if (cfg.stats) {
-        const uint32_t cap = (uint32_t)(cfg.sm_count * blocks_per_sm(k_primary<true>));
-        k_primary<true><<<need < cap ? need : cap, kThreads, 0, cfg.stream>>>(sc, cam, prm, accum, out, counters);
-    } else {
-        const uint32_t cap = (uint32_t)(cfg.sm_count * blocks_per_sm(k_primary<false>));
-        k_primary<false><<<need < cap ? need : cap, kThreads, 0, cfg.stream>>>(sc, cam, prm, accum, out, counters);
-    }
-    return cudaGetLastError();
+    if (coarse_in_smem(sc))
+        return cfg.stats ? run_primary<true, true>(sc, cam, prm, accum, out, counters, cfg)
+                         : run_primary<false, true>(sc, cam, prm, accum, out, counters, cfg);
+    return cfg.stats ? run_primary<true, false>(sc, cam, prm, accum, out, counters, cfg)
+                     : run_primary<false, false>(sc, cam, prm, accum, out, counters, cfg);
 }
 
 cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,
