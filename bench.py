@@ -212,12 +212,13 @@ def run_gpu(args, rank, world, local_rank):
     kern_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
     st = scene.stats()
     t = torch.tensor([step_ms], device=dev, dtype=torch.float64)
-    r = torch.tensor([float(st["rays"]), float(st["paths"])], device=dev, dtype=torch.float64)
+    r = torch.tensor([float(st["rays"]), float(st["paths"]), float(st["launches"])], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(r, op=dist.ReduceOp.SUM)
     step_ms = float(t[0]) / args.steps
     rays_per_step = float(r[0]) / args.steps
+    launches = int(r[2]) + (args.steps if rank == 0 or world == 1 else 0)      # + rank 0's resolve per step
     value = rays_per_step / (step_ms * 1e-3) / 1e6
 
     # ---- e2e: the blocking public call, host buffers, D2H of the frame inside the timed region ----
@@ -276,7 +277,7 @@ def run_gpu(args, rank, world, local_rank):
             "e2e": {"value": round(e2e_val, 2), "unit": "Mrays/s", "ms_per_frame": round(e2e_s * 1e3, 3),
                     "h2d_bytes_per_step": 56 + 48, "d2h_bytes_per_step": P * 3,
                     "note": "rtc_render(): host camera+params in, host RGB8 frame out; scene resident (uploaded once, like the reference's bakeInto before render)"},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": launches,
             "kernel_ms": {"k_path": round(kern_ms, 3)},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 5), "traffic": None,

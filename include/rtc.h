@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 1u
+#define RTC_ABI_VERSION 2u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -126,7 +126,7 @@ enum {
 
 /* Traversal selector (results are identical except in exact-t ties). */
 enum {
-    RTC_ACCEL_GRID = 0     /* uniform grid + 3D-DDA in the reference's cell order */
+    RTC_ACCEL_GRID = 0     /* uniform grid + 3D-DDA in the reference's cell order; resolution <= 1024 per axis */
 };
 
 /* Arithmetic contract. EXACT: no FMA contraction anywhere the reference has separate
@@ -162,6 +162,7 @@ typedef struct rtc_stats {
     uint64_t hits_shaded;    /* hits that fetched triangle data + 3 textures                 */
     uint64_t paths;          /* camera rays                                                  */
     double   kernel_ms;      /* device time of the render kernels of the last call           */
+    uint64_t launches;       /* kernels launched on the device since the counters were last read */
 } rtc_stats;
 
 /* Optional extra outputs (any pointer may be NULL). Host pointers. */

@@ -8,6 +8,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -81,6 +82,10 @@ struct rtc_scene {
     size_t h_pinned_bytes = 0;
     uint64_t num_tris = 0;
     uint32_t num_src_tris = 0;
+    // wavefront scratch (grown on demand) + kernels launched since the counters were last read
+    rtc::WaveScratch wave{};
+    std::vector<void*> wave_allocs;
+    uint64_t launches = 0;
 
     template <typename T>
     int alloc(T** out, size_t count)
@@ -260,6 +265,7 @@ void scene_free(rtc_scene* s)
     DeviceGuard guard(s->device);
     cudaDeviceSynchronize();
     for (void* p : s->allocs) cudaFree(p);
+    for (void* p : s->wave_allocs) cudaFree(p);
     cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
@@ -316,8 +322,8 @@ int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_param
     if (p->mode != RTC_MODE_PATH && p->mode != RTC_MODE_PRIMARY) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown mode %u", p->mode);
     if (p->accel != RTC_ACCEL_GRID) return fail(RTC_ERR_UNSUPPORTED, "unknown accel %u", p->accel);
     if (p->math != RTC_MATH_EXACT && p->math != RTC_MATH_FAST) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown math contract %u", p->math);
-    if (p->mode == RTC_MODE_PATH && p->max_bounce > 64)
-        return fail(RTC_ERR_UNSUPPORTED, "max_bounce %u > 64 (scatter stack capacity of the kernels)", (unsigned)p->max_bounce);
+    if (p->mode == RTC_MODE_PATH && p->max_bounce > rtc::kMaxBounce)
+        return fail(RTC_ERR_UNSUPPORTED, "max_bounce %u > %u (per-bounce queue bookkeeping of the kernels)", (unsigned)p->max_bounce, rtc::kMaxBounce);
     if (p->tile_world > 1 && p->tile_rank >= p->tile_world) return fail(RTC_ERR_INVALID_ARGUMENT, "tile_rank %u >= tile_world %u", p->tile_rank, p->tile_world);
     return RTC_OK;
 }
@@ -332,6 +338,53 @@ void shard_rows(const rtc_camera* cam, const rtc_params* p, uint32_t* y0, uint32
     *y1 = (uint32_t)(((uint64_t)cam->h * (p->tile_rank + 1)) / p->tile_world);
 }
 
+// Wavefront scratch for `slots` path slots and `levels` scattering levels (rtc_device.cuh WaveScratch).
+// The slot count is capped by a byte budget (RTC_WAVE_BYTES, default 6 GiB, at most half of the free HBM);
+// frames with more paths than slots are rendered in batches.
+int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels)
+{
+    if (levels < 1) levels = 1;
+    const size_t per_slot = 2 * 64 + sizeof(uint2) + sizeof(float4) + (size_t)levels * (sizeof(float4) + sizeof(float2));
+    size_t budget = (size_t)6 << 30;
+    if (const char* env = getenv("RTC_WAVE_BYTES")) { const long long v = atoll(env); if (v > 0) budget = (size_t)v; }
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+        size_t held = 0;
+        if (s->wave.cap) held = (size_t)s->wave.cap * (2 * 64 + sizeof(uint2) + sizeof(float4) + (size_t)s->wave.max_levels * 24);
+        if (budget > (free_b + held) / 2) budget = (free_b + held) / 2;
+    }
+    uint64_t want = pixels * (uint64_t)samples;
+    const uint64_t fit = budget / per_slot;
+    if (want > fit) want = fit;
+    if (want > 0x7FFFFFFFull) want = 0x7FFFFFFFull;
+    if (want < 1024) want = 1024;
+    if (s->wave.cap >= want && s->wave.max_levels >= levels) return RTC_OK;
+    for (void* p : s->wave_allocs) cudaFree(p);
+    s->wave_allocs.clear();
+    s->wave = rtc::WaveScratch{};
+    const size_t cap = (size_t)want;
+    auto grab = [&](void** out, size_t bytes) -> int {
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e != cudaSuccess) return fail(RTC_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes of wavefront scratch): %s", bytes, cudaGetErrorString(e));
+        s->wave_allocs.push_back(*out);
+        return RTC_OK;
+    };
+    rtc::WaveScratch w{};
+    for (int k = 0; k < 2; ++k) {
+        float4** arr[4] = { &w.q[k].a0, &w.q[k].a1, &w.q[k].a2, &w.q[k].a3 };
+        for (int j = 0; j < 4; ++j)
+            if (int rc = grab((void**)arr[j], cap * sizeof(float4))) return rc;
+    }
+    if (int rc = grab((void**)&w.hits, cap * sizeof(uint2))) return rc;
+    if (int rc = grab((void**)&w.stack_e, cap * levels * sizeof(float4))) return rc;
+    if (int rc = grab((void**)&w.stack_a, cap * levels * sizeof(float2))) return rc;
+    if (int rc = grab((void**)&w.leaf, cap * sizeof(float4))) return rc;
+    if (int rc = grab((void**)&w.counts, 2 * (rtc::kMaxBounce + 1) * sizeof(uint32_t))) return rc;
+    w.cap = (uint32_t)cap; w.max_levels = levels;
+    s->wave = w;
+    return RTC_OK;
+}
+
 int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, float4* accum,
                   rtc::PrimaryOut pout, cudaStream_t stream)
 {
@@ -341,15 +394,15 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
     dp.num_samples = p->num_samples; dp.max_bounce = p->max_bounce; dp.sample_offset = p->sample_offset;
     dp.seed_lo = (uint32_t)p->seed; dp.seed_hi = (uint32_t)(p->seed >> 32);
     dp.first_pixel = y0 * cam->w; dp.num_pixels = (y1 - y0) * cam->w;
+    const bool primary = p->mode == RTC_MODE_PRIMARY;
+    if (int rc = ensure_wave(s, dp.num_pixels, primary ? 1u : p->num_samples, primary ? 1u : p->max_bounce)) return rc;
     const rtc::DevCamera dc = to_dev(*cam);
     rtc::LaunchCfg cfg; cfg.sm_count = s->sm_count; cfg.stream = stream; cfg.stats = p->collect_stats != 0;
-    cudaError_t e;
-    if (p->mode == RTC_MODE_PRIMARY)
-        e = p->math == RTC_MATH_FAST ? rtc::fast::launch_primary(s->dev, dc, dp, accum, pout, s->counters, cfg)
-                                     : rtc::exact::launch_primary(s->dev, dc, dp, accum, pout, s->counters, cfg);
-    else
-        e = p->math == RTC_MATH_FAST ? rtc::fast::launch_path(s->dev, dc, dp, accum, s->counters, s->work, cfg)
-                                     : rtc::exact::launch_path(s->dev, dc, dp, accum, s->counters, s->work, cfg);
+    uint32_t launches = 0;
+    const cudaError_t e = p->math == RTC_MATH_FAST
+        ? rtc::fast::launch_render(s->dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches)
+        : rtc::exact::launch_render(s->dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches);
+    s->launches += launches;
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     return RTC_OK;
 }
@@ -379,6 +432,8 @@ int read_counters(rtc_scene* s, rtc_stats* out)
     CU(cudaMemset(s->counters, 0, sizeof c));
     out->rays = c[rtc::CNT_RAYS]; out->cells_visited = c[rtc::CNT_CELLS]; out->tris_tested = c[rtc::CNT_TRIS];
     out->hits_shaded = c[rtc::CNT_HITS]; out->paths = c[rtc::CNT_PATHS];
+    out->launches = s->launches;
+    s->launches = 0;
     return RTC_OK;
 }
 
@@ -410,6 +465,7 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t
         ? rtc::fast::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st)
         : rtc::exact::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
+    s->launches += 1;
     CU(cudaEventRecord(s->ev1, st));
     // D2H through the pinned staging buffer (rgb_out is pageable caller memory, src/main.zig:122).
     uint8_t* h_rgb = s->h_pinned;

@@ -60,6 +60,32 @@ struct DevParams {
     uint32_t first_pixel;    // pixel range of this call: [first_pixel, first_pixel + num_pixels)
     uint32_t num_pixels;
 };
+static constexpr uint32_t kMaxBounce = 64;
+
+// ---- wavefront scratch (HBM), sized for `cap` path slots; slot = sample_local * num_pixels + pixel_local ----
+// q[2]      : two ray queues (ping-pong per bounce), 64 B / ray as four float4 arrays (rtc_wavefront.cu QueuedRay)
+// hits      : uint2[cap]  per queue entry {t bits, baked triangle index | 0xFFFFFFFF}
+// stack_e/a : per scattering level and slot {emissive.xyz, albedo.x} {albedo.yz}        24 B / level
+// leaf      : float4[cap] value at the end of the path (sky / zeroes) + number of pushed levels
+// counts    : uint32[2*(kMaxBounce+1)]  queue length per bounce, then the chunk dispenser head per bounce
+struct RayQueue { float4 *a0, *a1, *a2, *a3; };
+struct WaveScratch {
+    RayQueue q[2];
+    uint2* hits;
+    float4* stack_e;
+    float2* stack_a;
+    float4* leaf;
+    uint32_t* counts;
+    uint32_t cap;
+    uint32_t max_levels;
+};
+// one batch: pixels [first_pixel, +num_pixels) x samples [s0, s0+ns) (absolute sample indices)
+struct WaveParams {
+    uint32_t first_pixel, num_pixels;
+    uint32_t s0, ns;
+    uint32_t max_bounce;
+    uint32_t seed_lo, seed_hi;
+};
 // counters[]: 0 rays, 1 cells_visited, 2 tris_tested, 3 hits_shaded, 4 paths
 enum { CNT_RAYS = 0, CNT_CELLS = 1, CNT_TRIS = 2, CNT_HITS = 3, CNT_PATHS = 4, CNT_N = 8 };
 
@@ -259,10 +285,10 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
     }
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
-__device__ __forceinline__ void rng_block(const DevParams& p, uint32_t pixel, uint32_t sample, uint32_t block, float out[4])
+__device__ __forceinline__ void rng_block(uint32_t seed_lo, uint32_t seed_hi, uint32_t pixel, uint32_t sample, uint32_t block, float out[4])
 {
     uint32_t r[4];
-    philox4x32_10(pixel, sample, block, 0u, p.seed_lo, p.seed_hi, r);
+    philox4x32_10(pixel, sample, block, 0u, seed_lo, seed_hi, r);
 #pragma unroll
     for (int i = 0; i < 4; ++i) out[i] = (float)(r[i] >> 8) * (1.0f / 16777216.0f);
 }

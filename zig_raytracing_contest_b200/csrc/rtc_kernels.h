@@ -1,4 +1,4 @@
-// rtc_kernels.h — launch entry points of the render kernels. rtc_kernels.cu is compiled twice,
+// rtc_kernels.h — launch entry points of the render kernels. rtc_wavefront.cu is compiled twice,
 // once per arithmetic contract (namespace exact: -fmad=false; namespace fast: -fmad=true).
 #pragma once
 #include "rtc_device.cuh"
@@ -18,15 +18,14 @@ struct PrimaryOut {
 
 #define RTC_DECLARE_LAUNCHERS(NS)                                                                     \
     namespace NS {                                                                                    \
-    /* renderWorker + traceRayRecursive (src/stage3.zig:188-245): adds prm.num_samples samples of   */ \
-    /* every pixel in [first_pixel, first_pixel+num_pixels) into accum[pixel] (rgb sum, count).     */ \
-    cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParams& prm,           \
-                            float4* accum, unsigned long long* counters, uint32_t* work,              \
-                            const LaunchCfg& cfg);                                                    \
-    /* deterministic slice: centre ray, depth 1 (hit -> emissive, miss -> sky) + hit buffers.        */ \
-    cudaError_t launch_primary(const DevScene& sc, const DevCamera& cam, const DevParams& prm,        \
-                               float4* accum, PrimaryOut out, unsigned long long* counters,           \
-                               const LaunchCfg& cfg);                                                 \
+    /* renderWorker + traceRayRecursive (src/stage3.zig:188-245) as a wavefront: adds                */ \
+    /* prm.num_samples samples of every pixel in [first_pixel, first_pixel+num_pixels) into          */ \
+    /* accum[pixel] (rgb sum, count). primary: the deterministic slice (centre ray, depth 1:         */ \
+    /* hit -> emissive, miss -> sky) + hit buffers. *launches += kernels launched.                   */ \
+    cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevParams& prm,         \
+                              bool primary, float4* accum, PrimaryOut out,                            \
+                              unsigned long long* counters, const WaveScratch& ws,                    \
+                              const LaunchCfg& cfg, uint32_t* launches);                              \
     /* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242).                                      */ \
     cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,      \
                                uint8_t* rgb, float* radiance, cudaStream_t stream);                   \

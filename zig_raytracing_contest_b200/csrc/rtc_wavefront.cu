@@ -1,0 +1,576 @@
+// rtc_wavefront.cu — sm_100a render kernels for the reference's per-pixel path-tracing loop
+// (src/stage3.zig:152-245), as a WAVEFRONT. Compiled twice: -DRTC_NS=exact -fmad=false and
+// -DRTC_NS=fast -fmad=true.
+//
+// A batch is a pixel range x a sample range = up to `cap` path slots. Per batch:
+//   k_gen     renderWorker's `camera.getRay(x + U, y + U)` (stage3.zig:238) + Grid.traceRay's DDA set-up
+//             (linalg.zig:443-469) for every slot -> ray queue 0
+//   per bounce d = 0 .. max_bounce-1:
+//     k_trace Scene.traceRay (stage3.zig:152-186) for every queued ray. Persistent warps; a lane whose ray
+//             ends writes its hit and IMMEDIATELY takes the next ray of the queue (no lane waits for the
+//             longest ray of its warp). Every lane walks its own DDA; the triangle tests of the 32 rays in
+//             flight are pooled and dealt out one (ray, triangle) pair per lane.
+//     k_shade the body of traceRayRecursive (stage3.zig:193-219) for every traced ray: sky on a miss, else
+//             attributes + textures + RNG; alpha pass-through or Lambertian scatter; survivors are
+//             ballot-compacted into the other ray queue (with their DDA set-up done here, at full lanes)
+//   k_accum   unwinds `emissive + albedo * recurse` innermost-first per path (the recursion's evaluation
+//             order) and adds the samples to the pixel in sample order (stage3.zig:237-241)
+// The first version of this path was one persistent megakernel (one lane = one path); its profile
+// (profiles/r1b_*) showed 16 of 32 lanes active and 25 % occupancy at 128 registers.
+#include "rtc_kernels.h"
+
+#ifndef RTC_NS
+#error "compile with -DRTC_NS=exact or -DRTC_NS=fast"
+#endif
+
+namespace rtc {
+namespace RTC_NS {
+
+static constexpr int kTraceThreads = 256;
+static constexpr int kTraceWarps = kTraceThreads / 32;
+static constexpr int kThreads = 256;                 // gen / shade / accum / resolve
+static constexpr uint32_t kMiss = 0xFFFFFFFFu;
+static constexpr uint32_t kFull = 0xFFFFFFFFu;
+#ifndef RTC_KMAXSTEP
+#define RTC_KMAXSTEP 8
+#endif
+static constexpr int kMaxStep = RTC_KMAXSTEP;        // DDA steps a lane may take per round before the pooled triangle pass
+static constexpr uint32_t kChunk = 64;               // queue entries a warp reserves per atomic
+
+// ---------------------------------------------------------------------------------------------------------
+// Grid.Iterator (src/linalg.zig:471-497) in a register-lean, branch-free form. The cell travels packed
+// (x | y<<10 | z<<20) next to the packed exit cell; t_delta carries the step direction in its sign bit.
+// The t_next_crossing / t_delta arithmetic is the reference's, add for add. `fine` is the occupancy mask
+// of the 4x4x4 block the cell lies in, `bi` that block's index (rtc_device.cuh).
+struct Trav {
+    float tx, ty, tz;                   // t_next_crossing
+    float dx, dy, dz;                   // |.| = t_delta; sign bit set = stepping towards 0 on that axis
+    uint32_t c, ec;                     // packed cell, packed exit cell
+    uint32_t bi;
+    unsigned long long fine;
+};
+
+static constexpr uint32_t kBlockBits = 0x3FCFF3FCu;    // bits 2..9 of each 10-bit field: the block coordinates
+
+template <bool CSM>
+__device__ __forceinline__ void trav_load_block(const DevScene& sc, const uint32_t* __restrict__ coarse, Trav& s)
+{
+    const uint32_t bx = (s.c >> 2) & 0xFFu, by = (s.c >> 12) & 0xFFu, bz = (s.c >> 22) & 0xFFu;
+    s.bi = bx + sc.nbx * (by + sc.nby * bz);
+    const uint32_t w = CSM ? coarse[s.bi >> 5] : __ldg(sc.coarse + (s.bi >> 5));
+    s.fine = ((w >> (s.bi & 31u)) & 1u) ? __ldg(sc.fine + s.bi) : 0ull;
+}
+// bit of the cell inside its block: x&3 | (y&3)<<2 | (z&3)<<4
+__device__ __forceinline__ uint32_t trav_cell_bit(uint32_t c) { return (c & 3u) | ((c >> 8) & 0xCu) | ((c >> 16) & 0x30u); }
+
+// Iterator.next: axis = {2,1,2,1,2,2,0,0}[(tx<ty)<<2 | (tx<tz)<<1 | (ty<tz)] (linalg.zig:479-484):
+// x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y). Returns +inf without
+// moving when the cell is the exit cell on that axis (linalg.zig:486-488).
+__device__ __forceinline__ float trav_next(Trav& s)
+{
+    const bool xy = s.tx < s.ty, xz = s.tx < s.tz, yz = s.ty < s.tz;
+    const bool ax = xy && xz, ay = !xy && yz, az = !ax && !ay;
+    const float t = ax ? s.tx : (ay ? s.ty : s.tz);
+    const float d = ax ? s.dx : (ay ? s.dy : s.dz);
+    const uint32_t m = ax ? 0x3FFu : (ay ? 0xFFC00u : 0x3FF00000u);
+    if (((s.c ^ s.ec) & m) == 0u) return __int_as_float(0x7f800000);
+    const uint32_t one = m & 0x00100401u;
+    s.c = (__float_as_uint(d) >> 31) ? s.c - one : s.c + one;
+    const float tn = t + fabsf(d);
+    s.tx = ax ? tn : s.tx; s.ty = ay ? tn : s.ty; s.tz = az ? tn : s.tz;
+    return t;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Ray queue entry (64 B, SoA over four float4 arrays): the ray and its DDA set-up.
+//   a0 = o.xyz | slot      a1 = d.xyz | packed cell      a2 = t_next.xyz | packed exit cell
+//   a3 = signed t_delta.xyz | scatter levels pushed so far
+struct QueuedRay {
+    Ray r;
+    uint32_t slot, top;
+    float tx, ty, tz, dx, dy, dz;
+    uint32_t c, ec;
+};
+__device__ __forceinline__ bool queue_setup(const DevScene& sc, const Ray& r, QueuedRay& q)
+{
+    GridIter it;
+    if (!grid_trace_ray(sc, r, it)) return false;
+    q.r = r;
+    q.tx = it.tx; q.ty = it.ty; q.tz = it.tz;
+    q.dx = __uint_as_float(__float_as_uint(it.dx) | (it.sx == 1u ? 0u : 0x80000000u));
+    q.dy = __uint_as_float(__float_as_uint(it.dy) | (it.sy == 1u ? 0u : 0x80000000u));
+    q.dz = __uint_as_float(__float_as_uint(it.dz) | (it.sz == 1u ? 0u : 0x80000000u));
+    q.c = it.cx | (it.cy << 10) | (it.cz << 20);
+    q.ec = it.ex | (it.ey << 10) | (it.ez << 20);
+    return true;
+}
+__device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const QueuedRay& e)
+{
+    q.a0[i] = make_float4(e.r.o.x, e.r.o.y, e.r.o.z, __uint_as_float(e.slot));
+    q.a1[i] = make_float4(e.r.d.x, e.r.d.y, e.r.d.z, __uint_as_float(e.c));
+    q.a2[i] = make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec));
+    q.a3[i] = make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.top));
+}
+// Appends the rays of the lanes with `push` to the queue: one atomic per warp, order within the warp kept.
+__device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, bool push, const QueuedRay& e)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t m = __ballot_sync(kFull, push);
+    if (m == 0u) return;
+    uint32_t base = 0;
+    if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(count, (uint32_t)__popc(m));
+    base = __shfl_sync(kFull, base, __ffs(m) - 1);
+    if (push) queue_store(q, base + __popc(m & ((1u << lane) - 1u)), e);
+}
+
+struct Counters { uint32_t rays, cells, tris, hits, paths; };
+__device__ __forceinline__ void flush_counters(const Counters& cn, unsigned long long* counters)
+{
+    uint32_t v[5] = { cn.rays, cn.cells, cn.tris, cn.hits, cn.paths };
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        unsigned long long x = v[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(kFull, x, o);
+        if ((threadIdx.x & 31) == 0 && x != 0) atomicAdd(counters + i, x);
+    }
+}
+
+// The coarse block bitmap staged in (dynamic) shared memory once per CTA; nullptr when it does not fit
+// (CSM = false: probed in global memory instead).
+template <bool CSM>
+__device__ __forceinline__ const uint32_t* stage_coarse(const DevScene& sc)
+{
+    extern __shared__ uint32_t s_coarse[];
+    if (!CSM) return nullptr;
+    for (uint32_t i = threadIdx.x; i < sc.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(sc.coarse + i);
+    __syncthreads();
+    return s_coarse;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_gen: one thread per path slot. slot = sample_local * num_pixels + pixel_local, so consecutive lanes are
+// consecutive pixels of a row (coherent primary rays). RNG block 0 of the path = the two jitter draws
+// (stage3.zig:238). PRIMARY: pixel centre, no RNG.
+template <bool PRIMARY>
+__global__ void __launch_bounds__(kThreads)
+k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam, const __grid_constant__ WaveParams wp,
+      const __grid_constant__ WaveScratch ws, PrimaryOut out, unsigned long long* __restrict__ counters)
+{
+    Counters cn = { 0, 0, 0, 0, 0 };
+    const uint32_t nslots = wp.num_pixels * wp.ns;
+    const uint32_t stride = gridDim.x * kThreads;
+    const uint32_t rounds = (nslots + stride - 1u) / stride;
+    for (uint32_t it = 0; it < rounds; ++it) {
+        const uint32_t slot = it * stride + blockIdx.x * kThreads + threadIdx.x;
+        const bool on = slot < nslots;
+        bool push = false;
+        QueuedRay e;
+        if (on) {
+            const uint32_t sl = slot / wp.num_pixels, pl = slot - sl * wp.num_pixels;
+            const uint32_t pixel = wp.first_pixel + pl;
+            const float x = (float)(pixel % cam.w), y = (float)(pixel / cam.w);
+            cn.paths += 1;
+            float4 leaf = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));     // depth == 0 -> zeroes (stage3.zig:189-191)
+            if (wp.max_bounce > 0u) {
+                Ray ray;
+                if (PRIMARY) {
+                    ray = camera_ray(cam, x + 0.5f, y + 0.5f);
+                } else {
+                    float jit[4];
+                    rng_block(wp.seed_lo, wp.seed_hi, pixel, wp.s0 + sl, 0u, jit);
+                    ray = camera_ray(cam, x + jit[0], y + jit[1]);
+                }
+                cn.rays += 1;
+                e.slot = slot; e.top = 0u;
+                push = queue_setup(sc, ray, e);
+                if (!push) {                                    // Grid.traceRay -> null: a miss (stage3.zig:159)
+                    const v3 sky = env_color(ray.d);
+                    leaf = make_float4(sky.x, sky.y, sky.z, __uint_as_float(0u));
+                    if (PRIMARY) {
+                        if (out.hit_id) out.hit_id[pixel] = kMiss;
+                        if (out.hit_tuv) {
+                            out.hit_tuv[3 * (size_t)pixel] = __int_as_float(0x7f800000);
+                            out.hit_tuv[3 * (size_t)pixel + 1] = 0.0f;
+                            out.hit_tuv[3 * (size_t)pixel + 2] = 0.0f;
+                        }
+                    }
+                }
+            }
+            if (!push) ws.leaf[slot] = leaf;
+        }
+        queue_push(ws.q[0], ws.counts, push, e);
+    }
+    flush_counters(cn, counters);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_trace: Scene.traceRay (src/stage3.zig:152-186) over a ray queue. Semantics per ray are the reference's:
+// cells in DDA order; within a cell the winner is the smallest (t, baked index) with t > 0, and it replaces
+// the running best only if strictly nearer — which is what the sequential `nearest.t > hit.t and hit.t > 0`
+// (stage3.zig:174) yields when triangles are tested in index order; the ray ends at the first cell whose
+// exit crossing is >= best.t (stage3.zig:179-182). The block occupancy masks only skip the cells[] load of
+// empty cells.
+struct TraceShared {
+    float4 ro[32];                      // per lane: ray origin (.w unused)
+    float4 rd[32];                      // per lane: ray direction
+    unsigned long long best[32];        // per lane: min over the cell's (t bits << 32 | baked triangle index)
+    uint2 item[32];                     // compacted pending list: {owner lane, begin - exclusive prefix}
+};
+
+template <bool STATS, bool CSM>
+__global__ void __launch_bounds__(kTraceThreads)
+k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* __restrict__ count_ptr,
+        uint32_t* __restrict__ head_ptr, uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
+{
+    __shared__ TraceShared s_ws[kTraceWarps];
+    const uint32_t* coarse = stage_coarse<CSM>(sc);
+    TraceShared& ws = s_ws[threadIdx.x >> 5];
+    const float inf = __int_as_float(0x7f800000);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u, le_mask = lt_mask | (1u << lane);
+    const uint32_t n = __ldg(count_ptr);
+    Counters cn = { 0, 0, 0, 0, 0 };
+    uint32_t next = 0, end = 0;         // the warp's reserved chunk of queue entries (uniform)
+    bool exhausted = false;             // uniform
+    bool alive = false;
+    Trav s;
+    float best_t = inf;
+    uint32_t best_tri = kMiss, qi = 0;
+    s.tx = s.ty = s.tz = s.dx = s.dy = s.dz = 0.0f; s.c = s.ec = s.bi = 0u; s.fine = 0ull;
+    for (;;) {
+        // ---- refill: idle lanes take the next rays of the queue ----
+        const uint32_t idle = __ballot_sync(kFull, !alive);
+        if (idle != 0u && !exhausted) {
+            if (next == end) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(head_ptr, kChunk);
+                base = __shfl_sync(kFull, base, 0);
+                if (base >= n) { exhausted = true; next = end = 0; }
+                else { next = base; end = base + kChunk < n ? base + kChunk : n; }
+            }
+            const uint32_t avail = end - next, want = __popc(idle);
+            const uint32_t take = want < avail ? want : avail;
+            if (!alive && (uint32_t)__popc(idle & lt_mask) < take) {
+                qi = next + __popc(idle & lt_mask);
+                const float4 a0 = __ldg(q.a0 + qi), a1 = __ldg(q.a1 + qi), a2 = __ldg(q.a2 + qi), a3 = __ldg(q.a3 + qi);
+                ws.ro[lane] = a0; ws.rd[lane] = a1;
+                s.tx = a2.x; s.ty = a2.y; s.tz = a2.z; s.dx = a3.x; s.dy = a3.y; s.dz = a3.z;
+                s.c = __float_as_uint(a1.w); s.ec = __float_as_uint(a2.w);
+                trav_load_block<CSM>(sc, coarse, s);
+                best_t = inf; best_tri = kMiss;
+                alive = true;
+            }
+            next += take;
+        }
+        if (__ballot_sync(kFull, alive) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- phase A: every live lane walks to its next non-empty cell (at most kMaxStep cells) ----
+        uint32_t begin = 0, cnt = 0;
+        bool done = false;
+        if (alive) {
+#pragma unroll 1
+            for (int k = 0; k < kMaxStep; ++k) {
+                if (STATS) cn.cells += 1;
+                const uint32_t b = trav_cell_bit(s.c);
+                if ((uint32_t)(s.fine >> b) & 1u) {
+                    const uint2 c = __ldg(sc.cells + (s.bi * 64u + b));
+                    begin = c.x; cnt = c.y - c.x;
+                    break;
+                }
+                const uint32_t c0 = s.c;
+                const float tn = trav_next(s);
+                if (best_t <= tn) { done = true; break; }
+                if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
+            }
+        }
+        if (STATS) cn.tris += cnt;
+        const uint32_t pend = __ballot_sync(kFull, cnt != 0u);
+        if (pend != 0u) {
+            // ---- phase B: pooled (ray, triangle) pairs, one per lane per pass ----
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, d); if (lane >= (uint32_t)d) incl += v; }
+            const uint32_t excl = incl - cnt;
+            const uint32_t total = __shfl_sync(kFull, incl, 31);
+            if (cnt != 0u) {
+                ws.item[__popc(pend & lt_mask)] = make_uint2(lane, begin - excl);
+                ws.best[lane] = ~0ull;
+            }
+            __syncwarp();
+            for (uint32_t base = 0; base < total; base += 32u) {
+                const bool mine = cnt != 0u && excl >= base && excl < base + 32u;
+                const uint32_t starts = __reduce_or_sync(kFull, mine ? 1u << (excl - base) : 0u);
+                const uint32_t before = __popc(__ballot_sync(kFull, cnt != 0u && excl < base));
+                const uint32_t j = base + lane;
+                if (j < total) {
+                    const uint2 it = ws.item[before + __popc(starts & le_mask) - 1u];
+                    const uint32_t ti = j + it.y;
+                    const float4 a = __ldg(sc.tri_v0 + ti), b = __ldg(sc.tri_e1 + ti), c = __ldg(sc.tri_e2 + ti);
+                    const float4 o4 = ws.ro[it.x], d4 = ws.rd[it.x];
+                    Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
+                    float t, u, v;
+                    if (tri_ray(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), r, t, u, v) && t > 0.0f)
+                        atomicMin(&ws.best[it.x], ((unsigned long long)__float_as_uint(t) << 32) | ti);
+                }
+            }
+            __syncwarp();
+            // ---- phase C: owners fold the cell's winner in and take the cell's exit crossing ----
+            if (cnt != 0u) {
+                const unsigned long long k = ws.best[lane];
+                const float t = __uint_as_float((uint32_t)(k >> 32));
+                if (k != ~0ull && best_t > t) { best_t = t; best_tri = (uint32_t)k; }
+                const uint32_t c0 = s.c;
+                const float tn = trav_next(s);
+                if (best_t <= tn) done = true;
+                else if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
+            }
+            __syncwarp();
+        }
+        if (done) {
+            hits[qi] = make_uint2(__float_as_uint(best_t), best_tri);
+            alive = false;
+        }
+    }
+    if (STATS) flush_counters(cn, counters);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Triangle.Data (src/stage3.zig:42-71) as stored on the device: 5 float4 per SOURCE triangle.
+struct TriData { v3 n0, n1, n2; float uv0[2], uv1[2], uv2[2]; uint32_t material; };
+__device__ __forceinline__ TriData load_tri_data(const DevScene& sc, uint32_t src)
+{
+    const float4* p = sc.tri_data + 5u * (size_t)src;
+    const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2), q3 = __ldg(p + 3);
+    TriData d;
+    d.n0 = mk(q0.x, q0.y, q0.z); d.n1 = mk(q0.w, q1.x, q1.y); d.n2 = mk(q1.z, q1.w, q2.x);
+    d.uv0[0] = q2.y; d.uv0[1] = q2.z; d.uv1[0] = q2.w; d.uv1[1] = q3.x; d.uv2[0] = q3.y; d.uv2[1] = q3.z;
+    d.material = __float_as_uint(q3.w);
+    return d;
+}
+// Triangle.Data.interpolate (src/stage3.zig:53-71), evaluation order as written.
+__device__ __forceinline__ v3 interp_normal(const TriData& d, float u, float v)
+{
+    const float w = 1.0f - u - v;
+    return (scale(d.n0, w) + scale(d.n1, u)) + scale(d.n2, v);
+}
+__device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, float& tu, float& tv)
+{
+    const float w = 1.0f - u - v;
+    tu = d.uv0[0] * w + d.uv1[0] * u + d.uv2[0] * v;
+    tv = d.uv0[1] * w + d.uv1[1] * u + d.uv2[1] * v;
+}
+
+// k_shade: the body of traceRayRecursive (src/stage3.zig:193-219) for every ray of bounce `bounce`. The hit's
+// u, v are recomputed from the winning triangle with the arithmetic of the test (same inputs, same bits).
+// RNG block 1 + bounce of the path: draw 0 = the alpha test (always drawn, stage3.zig:207), draws 1, 2 = the
+// scatter direction. A scattering level pushes (emissive, albedo) for k_accum; an alpha pass-through level
+// (stage3.zig:207-213) consumes a depth level and neither attenuates nor pushes.
+template <bool PRIMARY>
+__global__ void __launch_bounds__(kThreads)
+k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam, const __grid_constant__ WaveParams wp,
+        const __grid_constant__ WaveScratch ws, uint32_t bounce, PrimaryOut out, unsigned long long* __restrict__ counters)
+{
+    Counters cn = { 0, 0, 0, 0, 0 };
+    const RayQueue qin = ws.q[bounce & 1u], qout = ws.q[(bounce + 1u) & 1u];
+    const uint32_t n = __ldg(ws.counts + bounce);
+    const uint32_t stride = gridDim.x * kThreads;
+    const uint32_t rounds = (n + stride - 1u) / stride;
+    const float eps = 1.1920928955078125e-07f;           // std.math.floatEps(f32)
+    for (uint32_t it = 0; it < rounds; ++it) {
+        const uint32_t i = it * stride + blockIdx.x * kThreads + threadIdx.x;
+        bool push = false;
+        QueuedRay e;
+        if (i < n) {
+            const float4 a0 = __ldg(qin.a0 + i), a1 = __ldg(qin.a1 + i);
+            const uint2 h = __ldg(ws.hits + i);
+            const uint32_t slot = __float_as_uint(a0.w);
+            uint32_t top = __float_as_uint(__ldg(&qin.a3[i].w));
+            Ray ray; ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
+            const uint32_t sl = slot / wp.num_pixels, pl = slot - sl * wp.num_pixels;
+            const uint32_t pixel = wp.first_pixel + pl;
+            v3 leaf = splat(0.0f);
+            if (h.y == kMiss) {
+                leaf = env_color(ray.d);
+                if (PRIMARY) {
+                    if (out.hit_id) out.hit_id[pixel] = kMiss;
+                    if (out.hit_tuv) {
+                        out.hit_tuv[3 * (size_t)pixel] = __uint_as_float(h.x);
+                        out.hit_tuv[3 * (size_t)pixel + 1] = 0.0f;
+                        out.hit_tuv[3 * (size_t)pixel + 2] = 0.0f;
+                    }
+                }
+            } else {
+                cn.hits += 1;
+                const float4 ta = __ldg(sc.tri_v0 + h.y), tb = __ldg(sc.tri_e1 + h.y), tc = __ldg(sc.tri_e2 + h.y);
+                float t, u, v;
+                tri_ray(mk(ta.x, ta.y, ta.z), mk(tb.x, tb.y, tb.z), mk(tc.x, tc.y, tc.z), ray, t, u, v);
+                t = __uint_as_float(h.x);
+                const uint32_t src = __float_as_uint(ta.w);
+                const TriData td = load_tri_data(sc, src);
+                const DevMaterial* m = sc.materials + td.material;
+                float tu, tv;
+                interp_uv(td, u, v, tu, tv);
+                if (PRIMARY) {
+                    // depth-1 slice: traceRayRecursive(ray, 1) = emissive + albedo * zeroes
+                    leaf = tex_sample3(m->emissive, tu, tv);
+                    if (out.hit_id) out.hit_id[pixel] = src;
+                    if (out.hit_tuv) {
+                        out.hit_tuv[3 * (size_t)pixel] = t;
+                        out.hit_tuv[3 * (size_t)pixel + 1] = u;
+                        out.hit_tuv[3 * (size_t)pixel + 2] = v;
+                    }
+                } else {
+                    const v3 albedo = tex_sample3(m->base, tu, tv);
+                    const v3 emissive = tex_sample3(m->emissive, tu, tv);
+                    const float transparency = tex_sample1(m->alpha, tu, tv);
+                    const v3 normal = interp_normal(td, u, v);
+                    float rnd[4];
+                    rng_block(wp.seed_lo, wp.seed_hi, pixel, wp.s0 + sl, 1u + bounce, rnd);
+                    ray.o = ray_at(ray, t + eps);
+                    if (!(rnd[0] > transparency)) {          // scatter (stage3.zig:214-219)
+                        ray.d = normalize(normal + unit_vector(rnd[1], rnd[2]));
+                        const size_t k = (size_t)top * ws.cap + slot;
+                        ws.stack_e[k] = make_float4(emissive.x, emissive.y, emissive.z, albedo.x);
+                        ws.stack_a[k] = make_float2(albedo.y, albedo.z);
+                        top += 1u;
+                    }
+                    if (bounce + 1u < wp.max_bounce) {       // depth - 1 > 0: the recursion goes on
+                        cn.rays += 1;
+                        e.slot = slot; e.top = top;
+                        push = queue_setup(sc, ray, e);
+                        if (!push) leaf = env_color(ray.d);
+                    }
+                }
+            }
+            if (!push) ws.leaf[slot] = make_float4(leaf.x, leaf.y, leaf.z, __uint_as_float(top));
+        }
+        queue_push(qout, ws.counts + bounce + 1u, push, e);
+    }
+    flush_counters(cn, counters);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_accum: one thread per pixel of the batch. For every sample in order: value = leaf; then
+// value = emissive + albedo * value from the innermost scattering level outwards (the float evaluation
+// order of `emissive.add(albedo.mul(traceRayRecursive(...)))`, stage3.zig:219); pixel = pixel.add(value)
+// (stage3.zig:239-240). The running sum continues from accum[], so sample ranges rendered by successive
+// batches or calls add up in the reference's order.
+__global__ void __launch_bounds__(kThreads)
+k_accum(const __grid_constant__ WaveParams wp, const __grid_constant__ WaveScratch ws, float4* __restrict__ accum)
+{
+    const uint32_t pl = blockIdx.x * kThreads + threadIdx.x;
+    if (pl >= wp.num_pixels) return;
+    float4 a = accum[wp.first_pixel + pl];
+    for (uint32_t sl = 0; sl < wp.ns; ++sl) {
+        const uint32_t slot = sl * wp.num_pixels + pl;
+        const float4 lf = ws.leaf[slot];
+        v3 value = mk(lf.x, lf.y, lf.z);
+        for (uint32_t l = __float_as_uint(lf.w); l > 0u; --l) {
+            const size_t k = (size_t)(l - 1u) * ws.cap + slot;
+            const float4 ea = ws.stack_e[k];
+            const float2 a2 = ws.stack_a[k];
+            value = mk(ea.x, ea.y, ea.z) + mk(ea.w, a2.x, a2.y) * value;
+        }
+        a.x = a.x + value.x; a.y = a.y + value.y; a.z = a.z + value.z;
+    }
+    a.w = a.w + (float)wp.ns;
+    accum[wp.first_pixel + pl] = a;
+}
+
+// img[i] = pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:223,242):
+// inv = 1/(f32)S computed once, then multiplied.
+__global__ void __launch_bounds__(kThreads)
+k_resolve(const float4* __restrict__ accum, uint32_t num_pixels, uint32_t total_samples,
+          uint8_t* __restrict__ rgb, float* __restrict__ radiance)
+{
+    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= num_pixels) return;
+    const float inv = 1.0f / (float)total_samples;
+    const float4 a = accum[i];
+    const float r = a.x * inv, g = a.y * inv, b = a.z * inv;
+    if (radiance) { radiance[3 * (size_t)i] = r; radiance[3 * (size_t)i + 1] = g; radiance[3 * (size_t)i + 2] = b; }
+    if (rgb) {
+        rgb[3 * (size_t)i] = (uint8_t)to_rgb8(r);
+        rgb[3 * (size_t)i + 1] = (uint8_t)to_rgb8(g);
+        rgb[3 * (size_t)i + 2] = (uint8_t)to_rgb8(b);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+template <typename K>
+static int blocks_per_sm(K kernel, int threads, size_t smem)
+{
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem) != cudaSuccess || n < 1) n = 1;
+    return n;
+}
+
+template <bool STATS, bool CSM>
+static void run_trace(const DevScene& sc, const WaveScratch& ws, uint32_t bounce, unsigned long long* counters, const LaunchCfg& cfg)
+{
+    auto kern = k_trace<STATS, CSM>;
+    const size_t smem = CSM ? sc.coarse_words * sizeof(uint32_t) : 0;
+    static int per_sm[2] = { 0, 0 };                 // occupancy query cached per coarse-bitmap size class
+    static size_t per_sm_smem[2] = { ~(size_t)0, ~(size_t)0 };
+    if (per_sm_smem[STATS] != smem) { per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); per_sm_smem[STATS] = smem; }
+    kern<<<cfg.sm_count * per_sm[STATS], kTraceThreads, smem, cfg.stream>>>(sc, ws.q[bounce & 1u], ws.counts + bounce,
+                                                                             ws.counts + kMaxBounce + 1 + bounce, ws.hits, counters);
+}
+
+cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevParams& prm, bool primary, float4* accum,
+                          PrimaryOut out, unsigned long long* counters, const WaveScratch& ws, const LaunchCfg& cfg,
+                          uint32_t* launches)
+{
+    if (prm.num_pixels == 0 || (!primary && prm.num_samples == 0)) return cudaSuccess;
+    const uint32_t S = primary ? 1u : prm.num_samples;
+    const uint32_t B = primary ? 1u : prm.max_bounce;
+    if (B > kMaxBounce || B > ws.max_levels || ws.cap == 0) return cudaErrorInvalidValue;
+    const bool csm = sc.coarse_words <= kCoarseSmemMaxWords;
+    const int wide = cfg.sm_count * 8;                // grid-stride kernels: 8 CTAs of 256 threads per SM
+    // batches: pixel chunks of at most cap pixels x as many samples as fit into cap slots
+    const uint32_t px_chunk = prm.num_pixels < ws.cap ? prm.num_pixels : ws.cap;
+    for (uint32_t p0 = 0; p0 < prm.num_pixels; p0 += px_chunk) {
+        const uint32_t np = prm.num_pixels - p0 < px_chunk ? prm.num_pixels - p0 : px_chunk;
+        const uint32_t s_chunk = ws.cap / np < S ? ws.cap / np : S;
+        for (uint32_t s0 = 0; s0 < S; s0 += s_chunk) {
+            WaveParams wp;
+            wp.first_pixel = prm.first_pixel + p0; wp.num_pixels = np;
+            wp.s0 = prm.sample_offset + s0; wp.ns = S - s0 < s_chunk ? S - s0 : s_chunk;
+            wp.max_bounce = B; wp.seed_lo = prm.seed_lo; wp.seed_hi = prm.seed_hi;
+            cudaError_t e = cudaMemsetAsync(ws.counts, 0, 2 * (kMaxBounce + 1) * sizeof(uint32_t), cfg.stream);
+            if (e != cudaSuccess) return e;
+            const uint32_t nslots = wp.num_pixels * wp.ns;
+            const uint32_t need = (nslots + kThreads - 1) / kThreads;
+            const uint32_t g = need < (uint32_t)wide ? need : (uint32_t)wide;
+            if (primary) k_gen<true><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, out, counters);
+            else         k_gen<false><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, out, counters);
+            *launches += 1;
+            for (uint32_t b = 0; b < B; ++b) {
+                if (csm) { if (cfg.stats) run_trace<true, true>(sc, ws, b, counters, cfg); else run_trace<false, true>(sc, ws, b, counters, cfg); }
+                else     { if (cfg.stats) run_trace<true, false>(sc, ws, b, counters, cfg); else run_trace<false, false>(sc, ws, b, counters, cfg); }
+                if (primary) k_shade<true><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, b, out, counters);
+                else         k_shade<false><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, b, out, counters);
+                *launches += 2;
+            }
+            k_accum<<<(wp.num_pixels + kThreads - 1) / kThreads, kThreads, 0, cfg.stream>>>(wp, ws, accum);
+            *launches += 1;
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+        }
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,
+                           uint8_t* rgb, float* radiance, cudaStream_t stream)
+{
+    if (num_pixels == 0) return cudaSuccess;
+    k_resolve<<<(num_pixels + kThreads - 1) / kThreads, kThreads, 0, stream>>>(accum, num_pixels, total_samples, rgb, radiance);
+    return cudaGetLastError();
+}
+
+}  // namespace RTC_NS
+}  // namespace rtc

@@ -15,7 +15,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtc.so")
+LIB_PATH = os.environ.get("RTC_LIB_PATH") or os.path.join(_HERE, "librtc.so")   # override: kernel tuning builds only
 _LIB = None
 
 TRI_DATA_DTYPE = np.dtype([("normal", "<f4", (3, 3)), ("texcoord", "<f4", (3, 2)),
