@@ -36,6 +36,9 @@ WORKLOADS = {
 DEFAULT_WORKLOAD = "cfg3_atrium_1080p_64spp"
 SEED = 1
 OVERRIDE = {}      # --spp / --height (profiling runs only; the default line uses the workload as named)
+# dram__bytes_read.sum + dram__bytes_write.sum per k_trace launch from the committed `ncu --set full` capture
+# (profiles/); None until a capture of the current kernel exists.
+TRAFFIC = {}
 
 
 def build_workload(name):
@@ -217,6 +220,8 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(r, op=dist.ReduceOp.SUM)
     step_ms = float(t[0]) / args.steps
+    trace_ms = st["trace_ms"] / args.steps                     # rank 0's k_trace launches, CUDA events per launch
+    trace_launches = st["trace_launches"] / args.steps
     rays_per_step = float(r[0]) / args.steps
     launches = int(r[2]) + (args.steps if rank == 0 or world == 1 else 0)      # + rank 0's resolve per step
     value = rays_per_step / (step_ms * 1e-3) / 1e6
@@ -258,13 +263,14 @@ def run_gpu(args, rank, world, local_rank):
         scene.render_accumulate(cam, prm_s, acc.data_ptr(), stream)
         cs = scene.stats()
         algo_bytes = rtc.bytes_per_frame(cs, P)
+        trav_bytes = 8 * cs["cells_visited"] + 48 * cs["tris_tested"]      # k_trace's share: Cell + {v0,e1,e2} records
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        achieved = trav_bytes / (max(trace_ms, 1e-9) * 1e-3) / 1e9
         cfg = workload_config(args.workload, spec, geo, cam, spp, bounce, world)
         cfg["math"] = "exact (no FMA contraction)" if math == abi.RTC_MATH_EXACT else "fast (FMA contraction)"
         cfg["host_build_s"] = round(build_s, 3); cfg["scene_upload_s"] = round(upload_s, 3)
@@ -278,12 +284,19 @@ def run_gpu(args, rank, world, local_rank):
                     "h2d_bytes_per_step": 56 + 48, "d2h_bytes_per_step": P * 3,
                     "note": "rtc_render(): host camera+params in, host RGB8 frame out; scene resident (uploaded once, like the reference's bakeInto before render)"},
             "gpu_launches": launches,
-            "kernel_ms": {"k_path": round(kern_ms, 3)},
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 5), "traffic": None,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                         "algorithmic_bytes_per_launch": int(algo_bytes),
-                         "note": "k_path; bytes = 8/cell + 48/triangle test + 224/shaded hit + 3/pixel, counted by an instrumented launch of the same frame"},
+            "kernel_ms": {"render_kernels_per_step": round(kern_ms, 3), "k_trace_per_step": round(trace_ms, 3),
+                          "k_trace_share": round(trace_ms / max(kern_ms, 1e-9), 4)},
+            "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 5), "traffic": TRAFFIC.get(args.workload),
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "launches_per_step": round(trace_launches, 1),
+                         "avg_launch_ms": round(trace_ms / max(trace_launches, 1), 4),
+                         "algorithmic_bytes_per_launch": int(trav_bytes / max(trace_launches, 1)),
+                         "whole_frame": {"algorithmic_bytes": int(algo_bytes), "achieved": round(algo_bytes / (kern_ms * 1e-3) / 1e9, 2)},
+                         "note": "k_trace (traversal + intersection), one launch per bounce per batch; bytes = 8 per visited cell + 48 per "
+                                 "triangle test, counted by an instrumented run of the same frame; duration = CUDA events around every "
+                                 "k_trace launch of the timed steps. whole_frame adds 224 B per shaded hit + 3 B per pixel over all render kernels. "
+                                 "The scene is L2-resident, so this is algorithmic bytes against the HBM peak, not DRAM traffic"},
             "clocks": clocks.summary(),
         }
         if world == 1 and not args.no_cpu:

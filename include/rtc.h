@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 2u
+#define RTC_ABI_VERSION 3u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -163,6 +163,9 @@ typedef struct rtc_stats {
     uint64_t paths;          /* camera rays                                                  */
     double   kernel_ms;      /* device time of the render kernels of the last call           */
     uint64_t launches;       /* kernels launched on the device since the counters were last read */
+    double   trace_ms;       /* summed device time of the traversal kernel launches in that span  */
+    uint32_t trace_launches; /* ... how many launches that sum covers                            */
+    uint32_t trace_launches_untimed;
 } rtc_stats;
 
 /* Optional extra outputs (any pointer may be NULL). Host pointers. */

@@ -59,10 +59,17 @@ def main():
     ap.add_argument("report")
     ap.add_argument("--so", default="zig_raytracing_contest_b200/csrc/build")
     ap.add_argument("--top", type=int, default=40)
+    ap.add_argument("--launch", type=int, default=0, help="which captured launch of the report (0-based)")
     ap.add_argument("--kernel", default=None, help="substring of the mangled kernel name (default: from the report)")
     a = ap.parse_args()
     raw = subprocess.run(["ncu", "-i", a.report, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
+    starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]       # one block per captured launch
+    if a.launch >= len(starts):
+        sys.exit("report holds %d launches" % len(starts))
+    lo = starts[a.launch]
+    hi = starts[a.launch + 1] if a.launch + 1 < len(starts) else len(rows)
+    rows = rows[lo:hi]
     kname = rows[0][1]
     hdr = rows[1]
     col = {h: i for i, h in enumerate(hdr)}

@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 2
+RTC_ABI_VERSION = 3
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -86,7 +86,8 @@ class Params(C.Structure):        # rtc_params
 class Stats(C.Structure):         # rtc_stats
     _fields_ = [("rays", C.c_uint64), ("cells_visited", C.c_uint64),
                 ("tris_tested", C.c_uint64), ("hits_shaded", C.c_uint64),
-                ("paths", C.c_uint64), ("kernel_ms", C.c_double), ("launches", C.c_uint64)]
+                ("paths", C.c_uint64), ("kernel_ms", C.c_double), ("launches", C.c_uint64),
+                ("trace_ms", C.c_double), ("trace_launches", C.c_uint32), ("trace_launches_untimed", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

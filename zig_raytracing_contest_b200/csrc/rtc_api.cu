@@ -85,7 +85,10 @@ struct rtc_scene {
     // wavefront scratch (grown on demand) + kernels launched since the counters were last read
     rtc::WaveScratch wave{};
     std::vector<void*> wave_allocs;
+    bool wave_budget_limited = false;
     uint64_t launches = 0;
+    std::vector<cudaEvent_t> timer_events;
+    rtc::TraceTimer timer{};
 
     template <typename T>
     int alloc(T** out, size_t count)
@@ -244,7 +247,7 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;
     CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
-    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.nbx = nbx; d.nby = nby; d.coarse_words = (uint32_t)coarse.size();
+    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.nbx = nbx; d.nby = nby; d.nbxy = nbx * nby; d.coarse_words = (uint32_t)coarse.size();
     d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
     d.num_materials = desc->num_materials;
     s->num_tris = desc->num_tris;
@@ -256,6 +259,9 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
+    s->timer_events.resize(2 * 4096);
+    for (cudaEvent_t& e : s->timer_events) CU(cudaEventCreate(&e));
+    s->timer.ev = s->timer_events.data(); s->timer.capacity = 4096; s->timer.used = 0; s->timer.dropped = 0;
     return RTC_OK;
 }
 
@@ -268,6 +274,7 @@ void scene_free(rtc_scene* s)
     for (void* p : s->wave_allocs) cudaFree(p);
     cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    for (cudaEvent_t e : s->timer_events) cudaEventDestroy(e);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -344,6 +351,10 @@ void shard_rows(const rtc_camera* cam, const rtc_params* p, uint32_t* y0, uint32
 int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels)
 {
     if (levels < 1) levels = 1;
+    // fast path: the scratch already holds this frame, or is already as large as the budget allowed
+    if (s->wave.cap && s->wave.max_levels >= levels &&
+        (s->wave.cap >= pixels * (uint64_t)samples || (s->wave_budget_limited && s->wave.max_levels == levels)))
+        return RTC_OK;
     const size_t per_slot = 2 * 64 + sizeof(uint2) + sizeof(float4) + (size_t)levels * (sizeof(float4) + sizeof(float2));
     size_t budget = (size_t)6 << 30;
     if (const char* env = getenv("RTC_WAVE_BYTES")) { const long long v = atoll(env); if (v > 0) budget = (size_t)v; }
@@ -355,6 +366,7 @@ int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels
     }
     uint64_t want = pixels * (uint64_t)samples;
     const uint64_t fit = budget / per_slot;
+    const bool limited = want > fit;
     if (want > fit) want = fit;
     if (want > 0x7FFFFFFFull) want = 0x7FFFFFFFull;
     if (want < 1024) want = 1024;
@@ -382,6 +394,7 @@ int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels
     if (int rc = grab((void**)&w.counts, 2 * (rtc::kMaxBounce + 1) * sizeof(uint32_t))) return rc;
     w.cap = (uint32_t)cap; w.max_levels = levels;
     s->wave = w;
+    s->wave_budget_limited = limited;
     return RTC_OK;
 }
 
@@ -398,6 +411,7 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
     if (int rc = ensure_wave(s, dp.num_pixels, primary ? 1u : p->num_samples, primary ? 1u : p->max_bounce)) return rc;
     const rtc::DevCamera dc = to_dev(*cam);
     rtc::LaunchCfg cfg; cfg.sm_count = s->sm_count; cfg.stream = stream; cfg.stats = p->collect_stats != 0;
+    cfg.timer = &s->timer;
     uint32_t launches = 0;
     const cudaError_t e = p->math == RTC_MATH_FAST
         ? rtc::fast::launch_render(s->dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches)
@@ -434,6 +448,18 @@ int read_counters(rtc_scene* s, rtc_stats* out)
     out->hits_shaded = c[rtc::CNT_HITS]; out->paths = c[rtc::CNT_PATHS];
     out->launches = s->launches;
     s->launches = 0;
+    // k_trace brackets (the caller has synchronised the stream the launches went to)
+    double ms = 0.0;
+    uint32_t timed = 0;
+    for (uint32_t i = 0; i < s->timer.used; ++i) {
+        float t = 0.0f;
+        if (cudaEventElapsedTime(&t, s->timer.ev[2 * i], s->timer.ev[2 * i + 1]) == cudaSuccess) { ms += t; timed += 1; }
+        else cudaGetLastError();
+    }
+    out->trace_ms = ms;
+    out->trace_launches = timed;
+    out->trace_launches_untimed = s->timer.dropped;
+    s->timer.used = 0; s->timer.dropped = 0;
     return RTC_OK;
 }
 

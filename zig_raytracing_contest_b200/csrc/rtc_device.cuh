@@ -42,7 +42,7 @@ struct DevScene {
     const DevMaterial* materials;
     const unsigned long long* fine;
     const uint32_t* coarse;
-    uint32_t nbx, nby;          // blocks along x and y
+    uint32_t nbx, nby, nbxy;    // blocks along x and y; nbx*nby
     uint32_t coarse_words;
     uint32_t num_materials;
 };

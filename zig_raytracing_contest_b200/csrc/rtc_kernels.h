@@ -5,10 +5,20 @@
 
 namespace rtc {
 
+// CUDA-event brackets around every k_trace launch (the dominant kernel): the roofline's denominator is
+// measured live, on the launching stream, per launch. Pairs are read and recycled at rtc_scene_stats().
+struct TraceTimer {
+    cudaEvent_t* ev;       // 2 * capacity events
+    uint32_t capacity;
+    uint32_t used;         // pairs recorded since the last read
+    uint32_t dropped;      // launches not bracketed because the pool was full
+};
+
 struct LaunchCfg {
     int sm_count;          // SMs of the device the launch goes to
     cudaStream_t stream;
     bool stats;            // instrumented variant (cells/tris counters)
+    TraceTimer* timer;     // may be null
 };
 
 struct PrimaryOut {

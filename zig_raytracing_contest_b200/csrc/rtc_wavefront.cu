@@ -516,8 +516,13 @@ static void run_trace(const DevScene& sc, const WaveScratch& ws, uint32_t bounce
     static int per_sm[2] = { 0, 0 };                 // occupancy query cached per coarse-bitmap size class
     static size_t per_sm_smem[2] = { ~(size_t)0, ~(size_t)0 };
     if (per_sm_smem[STATS] != smem) { per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); per_sm_smem[STATS] = smem; }
+    TraceTimer* tm = cfg.timer;
+    const bool timed = tm && tm->used < tm->capacity;
+    if (tm && !timed) tm->dropped += 1;
+    if (timed) cudaEventRecord(tm->ev[2 * tm->used], cfg.stream);
     kern<<<cfg.sm_count * per_sm[STATS], kTraceThreads, smem, cfg.stream>>>(sc, ws.q[bounce & 1u], ws.counts + bounce,
                                                                              ws.counts + kMaxBounce + 1 + bounce, ws.hits, counters);
+    if (timed) { cudaEventRecord(tm->ev[2 * tm->used + 1], cfg.stream); tm->used += 1; }
 }
 
 cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevParams& prm, bool primary, float4* accum,

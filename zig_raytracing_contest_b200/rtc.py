@@ -52,7 +52,7 @@ def lib():
     L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
     L.rtc_geometry_free.argtypes = [C.POINTER(abi.Geometry)]
     L.rtc_geometry_free.restype = None
-    if L.rtc_abi_version() != abi.RTC_ABI_VERSION:
+    if L.rtc_abi_version() != abi.RTC_ABI_VERSION and not os.environ.get("RTC_SKIP_ABI_CHECK"):
         raise ImportError("librtc.so ABI %d != binding ABI %d" % (L.rtc_abi_version(), abi.RTC_ABI_VERSION))
     _LIB = L
     return L
