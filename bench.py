@@ -163,7 +163,7 @@ def workload_config(name, spec, geo, cam, spp, bounce, world):
 def run_gpu(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from zig_raytracing_contest_b200 import abi, rtc
+    from zig_raytracing_contest_b200 import abi, rtc, shard
     if rtc.device_count() < 1:
         raise SystemExit("bench.py: no sm_100 GPU visible and the render path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -176,8 +176,9 @@ def run_gpu(args, rank, world, local_rank):
     upload_s = time.perf_counter() - t0
     P = cam.w * cam.h
     math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
-    total = spp * world
-    prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, sample_offset=rank * spp, total_samples=total, math=math)
+    total = spp * world                             # weak scaling: the frame's sample count grows with N
+    s_off, s_cnt = shard.sample_shard(rank, world, total)
+    prm = rtc.make_params(num_samples=s_cnt, max_bounce=bounce, seed=SEED, sample_offset=s_off, total_samples=total, math=math)
     acc = torch.zeros(P, 4, device=dev)
     d_rgb = torch.zeros(P * 3, dtype=torch.uint8, device=dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
@@ -193,8 +194,7 @@ def run_gpu(args, rank, world, local_rank):
         if ev_k0: ev_k0.record()
         scene.render_accumulate(cam, prm, acc.data_ptr(), stream)
         if ev_k1: ev_k1.record()
-        if world > 1:
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+        shard.reduce_accumulators(acc, dst=0)       # the path's only collective (no-op at N = 1)
         if rank == 0:
             rtc.resolve(acc.data_ptr(), P, total, d_rgb.data_ptr(), None, device=local_rank, stream_ptr=stream)
 

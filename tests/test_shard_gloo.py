@@ -1,0 +1,87 @@
+"""The N>1 host path on CPU: two processes over gloo shard one frame by sample range (one
+reduce(SUM) of the accumulators) and by row band (one gather), with the CPU oracle standing in for the
+device render. Checks the partition arithmetic of zig_raytracing_contest_b200/shard.py, that the
+counter RNG makes the sharded frame equal the unsharded one, and the collective plumbing bench.py uses."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from zig_raytracing_contest_b200 import abi, rtc, scenes, shard
+
+
+def test_sample_shard_covers_every_sample_once():
+    for total in (1, 3, 64, 65, 4096):
+        for world in (1, 2, 3, 4, 8):
+            seen = []
+            for r in range(world):
+                off, cnt = shard.sample_shard(r, world, total)
+                seen += list(range(off, off + cnt))
+            assert seen == list(range(total))
+            counts = [shard.sample_shard(r, world, total)[1] for r in range(world)]
+            assert max(counts) - min(counts) <= 1
+    with pytest.raises(ValueError):
+        shard.sample_shard(2, 2, 8)
+
+
+def test_row_band_tiles_the_frame():
+    for h in (1, 7, 1080, 2160):
+        for world in (1, 2, 3, 8):
+            edges = [shard.row_band(r, world, h) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == h
+            assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle
+    spec = scenes.cornell(subdiv=2)
+    geo = rtc.Geometry(spec.positions, spec.tri_data, (8, 8, 8))
+    cam = spec.camera(height=27)
+    desc, keep = rtc.make_scene_desc(geo, spec.materials)
+    S, P = 6, cam.w * cam.h
+    # ---- sample ranges + reduce(SUM) ----
+    off, cnt = shard.sample_shard(rank, world, S)
+    prm = rtc.make_params(num_samples=cnt, max_bounce=3, seed=11, sample_offset=off, total_samples=S)
+    part = oracle.render(desc, cam, prm, num_threads=1)["radiance"]          # = (sum over my samples) / S
+    acc = torch.zeros(P, 4)
+    acc[:, :3] = torch.from_numpy(part.reshape(P, 3)) * S
+    acc[:, 3] = cnt
+    shard.reduce_accumulators(acc, dst=0)
+    # ---- row bands + gather ----
+    y0, y1 = shard.row_band(rank, world, cam.h)
+    full_prm = rtc.make_params(num_samples=S, max_bounce=3, seed=11)
+    band = oracle.render(desc, cam, full_prm, num_threads=1, rows=(y0, y1))["rgb"][y0:y1]
+    frame = shard.gather_row_bands(torch.from_numpy(band.copy()), cam.w, cam.h, dst=0)
+    if rank == 0:
+        ref = oracle.render(desc, cam, full_prm, num_threads=1)
+        np.save(os.path.join(out_dir, "acc.npy"), acc.numpy())
+        np.save(os.path.join(out_dir, "frame.npy"), frame.numpy())
+        np.save(os.path.join(out_dir, "ref_rad.npy"), ref["radiance"])
+        np.save(os.path.join(out_dir, "ref_rgb.npy"), ref["rgb"])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_reproduce_the_single_frame(tmp_path, orc):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    acc = np.load(tmp_path / "acc.npy")
+    ref_rad = np.load(tmp_path / "ref_rad.npy").reshape(-1, 3)
+    assert (acc[:, 3] == 6).all()                                    # every sample rendered exactly once
+    np.testing.assert_allclose(acc[:, :3] / 6.0, ref_rad, rtol=3e-6, atol=1e-7)   # fp32 sum reordering only
+    assert np.array_equal(np.load(tmp_path / "frame.npy"), np.load(tmp_path / "ref_rgb.npy"))

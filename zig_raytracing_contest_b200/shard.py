@@ -1,0 +1,61 @@
+"""Host-side sharding of one frame over ranks. One process per GPU, scene replicated.
+
+The reference splits pixels into contiguous ranges over worker threads with no communication
+(src/stage3.zig:228-233,247-255); samples of a pixel are independent as well because the RNG is
+keyed by absolute (pixel, sample). Two partitions, both without a collective inside the render:
+
+  sample ranges : rank r renders samples [offset, offset+count) of every pixel into a float4
+                  accumulator; ONE reduce(SUM) to rank 0, which resolves (1/S, toRGB)
+  row bands     : rank r renders rows [y0, y1) and the finished bands are gathered on rank 0
+
+Works with any torch.distributed backend (nccl on the GPUs, gloo in the CPU tests).
+"""
+import torch
+import torch.distributed as dist
+
+
+def sample_shard(rank, world, total_samples):
+    """Contiguous sample range of `rank`: (offset, count). The first total % world ranks get one more."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("rank %d of %d" % (rank, world))
+    base, extra = divmod(int(total_samples), world)
+    count = base + (1 if rank < extra else 0)
+    offset = rank * base + min(rank, extra)
+    return offset, count
+
+
+def row_band(rank, world, height):
+    """Rows [y0, y1) of `rank` — the same split rtc_render applies for tile_rank/tile_world
+    (csrc/rtc_api.cu shard_rows): y0 = h*r/n, y1 = h*(r+1)/n."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("rank %d of %d" % (rank, world))
+    return (height * rank) // world, (height * (rank + 1)) // world
+
+
+def reduce_accumulators(acc, dst=0, group=None):
+    """Sum the per-rank accumulators ([P,4] float32: rgb sum, sample count) onto rank `dst`, in place."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.reduce(acc, dst=dst, op=dist.ReduceOp.SUM, group=group)
+    return acc
+
+
+def gather_row_bands(band, width, height, dst=0, group=None):
+    """Assemble the frame from per-rank row bands. `band` is this rank's [y1-y0, width, C] tensor.
+    Returns the [height, width, C] frame on rank `dst`, None elsewhere."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if world == 1:
+        return band
+    # bands differ by at most one row: pad to the tallest so one gather of equal tensors does it
+    tallest = max(row_band(r, world, height)[1] - row_band(r, world, height)[0] for r in range(world))
+    padded = torch.zeros((tallest,) + tuple(band.shape[1:]), dtype=band.dtype, device=band.device)
+    padded[:band.shape[0]] = band
+    out = [torch.empty_like(padded) for _ in range(world)] if rank == dst else None
+    dist.gather(padded, out, dst=dst, group=group)
+    if rank != dst:
+        return None
+    frame = torch.empty((height, width) + tuple(band.shape[2:]), dtype=band.dtype, device=band.device)
+    for r in range(world):
+        y0, y1 = row_band(r, world, height)
+        frame[y0:y1] = out[r][:y1 - y0]
+    return frame
