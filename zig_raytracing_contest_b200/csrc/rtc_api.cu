@@ -167,9 +167,12 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
         if (g.resolution[a] > rtc::kMaxGridRes)
             return fail(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)",
                         g.resolution[a], a, rtc::kMaxGridRes);
-    // validate cells; re-lay them out block-major (4x4x4-cell blocks) and derive the two occupancy levels
+    // validate cells; re-lay them out by packed cell (rtc_device.cuh) and derive the two occupancy levels
     const uint32_t nbx = (g.resolution[0] + 3) / 4, nby = (g.resolution[1] + 3) / 4, nbz = (g.resolution[2] + 3) / 4;
-    const size_t nb = (size_t)nbx * nby * nbz;
+    auto clog2 = [](uint32_t n) { uint32_t l = 0; while ((1u << l) < n) ++l; return l; };
+    const uint32_t lx = clog2(nbx), ly = clog2(nby), lz = clog2(nbz);
+    uint32_t shift[3] = { 6u, 6u + lx, 6u + lx + ly };
+    const size_t nb = (size_t)1 << (lx + ly + lz);
     std::vector<rtc_cell> cells_b(nb * 64, rtc_cell{ 0u, 0u });
     std::vector<unsigned long long> fine(nb, 0ull);
     std::vector<uint32_t> coarse((nb + 31) / 32, 0u);
@@ -182,10 +185,10 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
                     if (cell.begin > cell.end || cell.end > desc->num_tris)
                         return fail(RTC_ERR_INVALID_ARGUMENT, "cell %llu has range [%u,%u) outside the %llu baked triangles",
                                     (unsigned long long)c, cell.begin, cell.end, (unsigned long long)desc->num_tris);
-                    const size_t bi = (x >> 2) + (size_t)nbx * ((y >> 2) + (size_t)nby * (z >> 2));
-                    const uint32_t b = (x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4);
-                    cells_b[bi * 64 + b] = cell;
-                    if (cell.end > cell.begin) { fine[bi] |= 1ull << b; coarse[bi >> 5] |= 1u << (bi & 31); }
+                    const uint32_t pc = rtc::pack_cell(shift, x, y, z);
+                    const size_t bi = pc >> 6;
+                    cells_b[pc] = cell;
+                    if (cell.end > cell.begin) { fine[bi] |= 1ull << (pc & 63u); coarse[bi >> 5] |= 1u << (bi & 31); }
                 }
     }
     uint32_t num_src = desc->num_src_tris;
@@ -247,7 +250,11 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;
     CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
-    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.nbx = nbx; d.nby = nby; d.nbxy = nbx * nby; d.coarse_words = (uint32_t)coarse.size();
+    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.coarse_words = (uint32_t)coarse.size();
+    d.mask[0] = 0x03u | (((1u << lx) - 1u) << shift[0]);
+    d.mask[1] = 0x0Cu | (((1u << ly) - 1u) << shift[1]);
+    d.mask[2] = 0x30u | (((1u << lz) - 1u) << shift[2]);
+    for (int a = 0; a < 3; ++a) d.shift[a] = shift[a];
     d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
     d.num_materials = desc->num_materials;
     s->num_tris = desc->num_tris;

@@ -13,13 +13,15 @@
 namespace rtc {
 
 // ---- device-side scene layout (HBM) ---------------------------------------------------
-// cells     : uint2[64*NB]  {begin,end}, 8 B / cell, BLOCK-MAJOR: the grid is cut into 4x4x4-cell blocks
-//             (NB = ceil(rx/4)*ceil(ry/4)*ceil(rz/4), x fastest); record = block*64 + (x&3 | (y&3)<<2 | (z&3)<<4)
-// fine      : uint64[NB]    bit b = cell b of the block is non-empty. One 8-byte load covers every DDA step a
+// PACKED CELL. A cell (x,y,z) travels as one 32-bit word
+//     x&3 | (y&3)<<2 | (z&3)<<4 | (x>>2)<<6 | (y>>2)<<(6+lx) | (z>>2)<<(6+lx+ly)
+// i.e. the low 6 bits are the cell inside its 4x4x4 block and word>>6 is the block index, with the block
+// grid padded to powers of two (lx, ly, lz = ceil(log2(blocks per axis))). mask[a] holds the bits of axis a.
+// The word IS the index of the cell's record, so nothing is recomputed from coordinates on the device.
+// cells     : uint2[64*NBP] {begin,end}, 8 B / cell, indexed by the packed cell (NBP = 2^(lx+ly+lz) blocks)
+// fine      : uint64[NBP]   bit b = cell b of the block is non-empty. One 8-byte load covers every DDA step a
 //             ray takes inside the block (the per-step occupancy probe was the top stall of the first kernel)
-// coarse    : uint32[NB/32] bit = block has any triangle; 4 KiB at 128^3 -> staged in shared memory per CTA
-// tri_v0/e1/e2 : float4[M] each (SoA) {v0.xyz, src id bits} {e1.xyz,0} {e2.xyz,0}   48 B / baked triangle;
-//             SoA so that 32 lanes testing 32 consecutive triangles issue three fully coalesced LDG.128
+// coarse    : uint32[NBP/32] bit = block has any triangle; 4 KiB at 128^3 -> staged in shared memory per CTA
 // tri_data  : float4[5*N]   per SOURCE triangle: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat | pad
 // texels    : float4[w*h] (rgb, pad) for base colour / emissive, float[w*h] for transparency
 struct DevTexture {
@@ -42,12 +44,17 @@ struct DevScene {
     const DevMaterial* materials;
     const unsigned long long* fine;
     const uint32_t* coarse;
-    uint32_t nbx, nby, nbxy;    // blocks along x and y; nbx*nby
+    uint32_t mask[3];           // bits of the packed cell that belong to x, y, z
+    uint32_t shift[3];          // bit position of the block coordinate of x, y, z (6, 6+lx, 6+lx+ly)
     uint32_t coarse_words;
     uint32_t num_materials;
 };
-static constexpr uint32_t kMaxGridRes = 1024;     // cell coordinates travel packed, 10 bits per axis
+static constexpr uint32_t kMaxGridRes = 1024;     // packed cell: 6 + 3*8 bits
 static constexpr uint32_t kCoarseSmemMaxWords = 8192;   // 32 KiB: the coarse bitmap of a 256^3 grid
+__host__ __device__ __forceinline__ uint32_t pack_cell(const uint32_t shift[3], uint32_t x, uint32_t y, uint32_t z)
+{
+    return (x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4) | ((x >> 2) << shift[0]) | ((y >> 2) << shift[1]) | ((z >> 2) << shift[2]);
+}
 struct DevCamera {
     uint32_t w, h;
     float origin[3], llc[3], right[3], up[3];

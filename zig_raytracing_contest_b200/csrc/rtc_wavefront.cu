@@ -31,6 +31,9 @@ static constexpr int kTraceWarps = kTraceThreads / 32;
 static constexpr int kThreads = 256;                 // gen / shade / accum / resolve
 static constexpr uint32_t kMiss = 0xFFFFFFFFu;
 static constexpr uint32_t kFull = 0xFFFFFFFFu;
+#ifndef RTC_TRACE_MINB
+#define RTC_TRACE_MINB 4
+#endif
 #ifndef RTC_KMAXSTEP
 #define RTC_KMAXSTEP 8
 #endif
@@ -38,46 +41,51 @@ static constexpr int kMaxStep = RTC_KMAXSTEP;        // DDA steps a lane may tak
 static constexpr uint32_t kChunk = 64;               // queue entries a warp reserves per atomic
 
 // ---------------------------------------------------------------------------------------------------------
-// Grid.Iterator (src/linalg.zig:471-497) in a register-lean, branch-free form. The cell travels packed
-// (x | y<<10 | z<<20) next to the packed exit cell; t_delta carries the step direction in its sign bit.
-// The t_next_crossing / t_delta arithmetic is the reference's, add for add. `fine` is the occupancy mask
-// of the 4x4x4 block the cell lies in, `bi` that block's index (rtc_device.cuh).
+// Grid.Iterator (src/linalg.zig:471-497) in a register-lean form. The cell travels as the packed word of
+// rtc_device.cuh (low 6 bits = cell inside its 4x4x4 block, the rest = block index) next to the packed exit
+// cell; t_delta carries the step direction in its sign bit. The t_next_crossing / t_delta arithmetic is the
+// reference's, add for add. fine_lo/hi = occupancy mask of the block the cell lies in.
 struct Trav {
     float tx, ty, tz;                   // t_next_crossing
     float dx, dy, dz;                   // |.| = t_delta; sign bit set = stepping towards 0 on that axis
     uint32_t c, ec;                     // packed cell, packed exit cell
-    uint32_t bi;
-    unsigned long long fine;
+    uint32_t fine_lo, fine_hi;
 };
 
-static constexpr uint32_t kBlockBits = 0x3FCFF3FCu;    // bits 2..9 of each 10-bit field: the block coordinates
-
+// Occupancy of the block of cell s.c: the coarse bit (shared memory when CSM) decides whether the 8-byte fine
+// mask is fetched at all.
 template <bool CSM>
 __device__ __forceinline__ void trav_load_block(const DevScene& sc, const uint32_t* __restrict__ coarse, Trav& s)
 {
-    const uint32_t bx = (s.c >> 2) & 0xFFu, by = (s.c >> 12) & 0xFFu, bz = (s.c >> 22) & 0xFFu;
-    s.bi = bx + sc.nbx * (by + sc.nby * bz);
-    const uint32_t w = CSM ? coarse[s.bi >> 5] : __ldg(sc.coarse + (s.bi >> 5));
-    s.fine = ((w >> (s.bi & 31u)) & 1u) ? __ldg(sc.fine + s.bi) : 0ull;
+    const uint32_t bi = s.c >> 6;
+    const uint32_t w = CSM ? coarse[bi >> 5] : __ldg(sc.coarse + (bi >> 5));
+    uint2 f = make_uint2(0u, 0u);
+    if ((w >> (bi & 31u)) & 1u) f = __ldg(reinterpret_cast<const uint2*>(sc.fine) + bi);
+    s.fine_lo = f.x; s.fine_hi = f.y;
 }
-// bit of the cell inside its block: x&3 | (y&3)<<2 | (z&3)<<4
-__device__ __forceinline__ uint32_t trav_cell_bit(uint32_t c) { return (c & 3u) | ((c >> 8) & 0xCu) | ((c >> 16) & 0x30u); }
+__device__ __forceinline__ bool trav_occupied(const Trav& s)
+{
+    const uint32_t w = (s.c & 32u) ? s.fine_hi : s.fine_lo;
+    return ((w >> (s.c & 31u)) & 1u) != 0u;
+}
 
 // Iterator.next: axis = {2,1,2,1,2,2,0,0}[(tx<ty)<<2 | (tx<tz)<<1 | (ty<tz)] (linalg.zig:479-484):
 // x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y). Returns +inf without
-// moving when the cell is the exit cell on that axis (linalg.zig:486-488).
-__device__ __forceinline__ float trav_next(Trav& s)
+// moving when the cell is the exit cell on that axis (linalg.zig:486-488). The coordinate of the axis is a
+// scattered bit field m of the packed cell: with every other bit set, +1 carries across the gap
+// ((c | ~m) + 1), and (c | ~m) + m == (c & m) - 1 is the decrement.
+__device__ __forceinline__ float trav_next(const DevScene& sc, Trav& s)
 {
     const bool xy = s.tx < s.ty, xz = s.tx < s.tz, yz = s.ty < s.tz;
-    const bool ax = xy && xz, ay = !xy && yz, az = !ax && !ay;
+    const bool ax = xy && xz, ay = !xy && yz;
     const float t = ax ? s.tx : (ay ? s.ty : s.tz);
     const float d = ax ? s.dx : (ay ? s.dy : s.dz);
-    const uint32_t m = ax ? 0x3FFu : (ay ? 0xFFC00u : 0x3FF00000u);
+    const uint32_t m = ax ? sc.mask[0] : (ay ? sc.mask[1] : sc.mask[2]);
     if (((s.c ^ s.ec) & m) == 0u) return __int_as_float(0x7f800000);
-    const uint32_t one = m & 0x00100401u;
-    s.c = (__float_as_uint(d) >> 31) ? s.c - one : s.c + one;
+    const uint32_t stepped = (s.c | ~m) + (__float_as_int(d) < 0 ? m : 1u);
+    s.c = (stepped & m) | (s.c & ~m);
     const float tn = t + fabsf(d);
-    s.tx = ax ? tn : s.tx; s.ty = ay ? tn : s.ty; s.tz = az ? tn : s.tz;
+    s.tx = ax ? tn : s.tx; s.ty = ay ? tn : s.ty; s.tz = ax ? s.tz : (ay ? s.tz : tn);
     return t;
 }
 
@@ -100,8 +108,8 @@ __device__ __forceinline__ bool queue_setup(const DevScene& sc, const Ray& r, Qu
     q.dx = __uint_as_float(__float_as_uint(it.dx) | (it.sx == 1u ? 0u : 0x80000000u));
     q.dy = __uint_as_float(__float_as_uint(it.dy) | (it.sy == 1u ? 0u : 0x80000000u));
     q.dz = __uint_as_float(__float_as_uint(it.dz) | (it.sz == 1u ? 0u : 0x80000000u));
-    q.c = it.cx | (it.cy << 10) | (it.cz << 20);
-    q.ec = it.ex | (it.ey << 10) | (it.ez << 20);
+    q.c = pack_cell(sc.shift, it.cx, it.cy, it.cz);
+    q.ec = pack_cell(sc.shift, it.ex, it.ey, it.ez);
     return true;
 }
 __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const QueuedRay& e)
@@ -219,7 +227,7 @@ struct TraceShared {
 };
 
 template <bool STATS, bool CSM>
-__global__ void __launch_bounds__(kTraceThreads)
+__global__ void __launch_bounds__(kTraceThreads, RTC_TRACE_MINB)
 k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* __restrict__ count_ptr,
         uint32_t* __restrict__ head_ptr, uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
@@ -237,7 +245,7 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
     Trav s;
     float best_t = inf;
     uint32_t best_tri = kMiss, qi = 0;
-    s.tx = s.ty = s.tz = s.dx = s.dy = s.dz = 0.0f; s.c = s.ec = s.bi = 0u; s.fine = 0ull;
+    s.tx = s.ty = s.tz = s.dx = s.dy = s.dz = 0.0f; s.c = s.ec = s.fine_lo = s.fine_hi = 0u;
     for (;;) {
         // ---- refill: idle lanes take the next rays of the queue ----
         const uint32_t idle = __ballot_sync(kFull, !alive);
@@ -274,16 +282,15 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 #pragma unroll 1
             for (int k = 0; k < kMaxStep; ++k) {
                 if (STATS) cn.cells += 1;
-                const uint32_t b = trav_cell_bit(s.c);
-                if ((uint32_t)(s.fine >> b) & 1u) {
-                    const uint2 c = __ldg(sc.cells + (s.bi * 64u + b));
+                if (trav_occupied(s)) {
+                    const uint2 c = __ldg(sc.cells + s.c);
                     begin = c.x; cnt = c.y - c.x;
                     break;
                 }
                 const uint32_t c0 = s.c;
-                const float tn = trav_next(s);
+                const float tn = trav_next(sc, s);
                 if (best_t <= tn) { done = true; break; }
-                if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
+                if ((s.c ^ c0) >> 6) trav_load_block<CSM>(sc, coarse, s);
             }
         }
         if (STATS) cn.tris += cnt;
@@ -323,9 +330,9 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                 const float t = __uint_as_float((uint32_t)(k >> 32));
                 if (k != ~0ull && best_t > t) { best_t = t; best_tri = (uint32_t)k; }
                 const uint32_t c0 = s.c;
-                const float tn = trav_next(s);
+                const float tn = trav_next(sc, s);
                 if (best_t <= tn) done = true;
-                else if ((s.c ^ c0) & kBlockBits) trav_load_block<CSM>(sc, coarse, s);
+                else if ((s.c ^ c0) >> 6) trav_load_block<CSM>(sc, coarse, s);
             }
             __syncwarp();
         }
