@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 3u
+#define RTC_ABI_VERSION 4u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -229,6 +229,46 @@ typedef struct rtc_geometry {
 int  rtc_geometry_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
                         const uint32_t grid_resolution[3], rtc_geometry* out);
 void rtc_geometry_free(rtc_geometry* g);
+
+/* ---- stage1 + main.zig's file contracts as the path's callers ---------
+ * Host-only (no GPU needed). These are what a host that is NOT the Zig program uses to honour the
+ * reference's input/output contract; the Zig host keeps zgltf + stb and needs none of them. */
+
+/* main.Config (src/main.zig:56-69): config.json, read from the cwd by the reference. */
+typedef struct rtc_config {
+    uint32_t grid_resolution[3];
+    uint32_t num_threads;      /* 0 = JSON null = all cores (src/main.zig:90) */
+    uint16_t num_samples;
+    uint16_t max_bounce;
+} rtc_config;
+int rtc_config_load(const char* path, rtc_config* out);
+
+/* What stage1 leaves in memory (src/main.zig:104-112): the camera, the material textures and the
+ * world-space triangle soup. Library-owned until rtc_host_scene_free. */
+typedef struct rtc_host_scene {
+    rtc_camera    camera;
+    float*        positions;     /* num_tris * 9: three world-space vertices per triangle          */
+    rtc_tri_data* tri_data;      /* num_tris records (src_tri = index in this soup)                */
+    uint32_t      num_tris;
+    rtc_material* materials;     /* num_materials, texels owned by the library                      */
+    uint32_t      num_materials;
+    uint32_t      num_images;
+    void*         owner;
+} rtc_host_scene;
+
+/* loadGltfFile + loadCamera + loadMaterials + loadGeometry (src/stage1.zig:75,261,309,485) for a
+ * .gltf (+ external buffers / PNG images / data: URIs) or .glb file. camera_name NULL = the first
+ * camera; width/height 0 = not given (size rules of src/stage1.zig:322-342). PNG textures are
+ * linearised like stb's stbi_loadf (pow(c/255, 2.2), alpha linear); JPEG is RTC_ERR_UNSUPPORTED. */
+int  rtc_gltf_load(const char* path, const char* camera_name, uint32_t width, uint32_t height,
+                   int num_threads, rtc_host_scene* out);
+void rtc_host_scene_free(rtc_host_scene* scene);
+
+/* stbi_write_png(path, w, h, 3, rgb, 3*w) of src/main.zig:130-135 (8-bit RGB, row 0 = top).
+ * Returns RTC_OK / RTC_ERR_IO (stb returns 1 / 0). */
+int  rtc_png_write(const char* path, uint32_t w, uint32_t h, const uint8_t* rgb);
+/* Decodes a PNG file to 8-bit RGB (the inverse, for tests and tools). rgb_out: malloc'ed, free with free(). */
+int  rtc_png_read(const char* path, uint32_t* w, uint32_t* h, uint8_t** rgb_out);
 
 /* ---- misc ------------------------------------------------------------------------ */
 

@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 3
+RTC_ABI_VERSION = 4
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -107,9 +107,23 @@ class Geometry(C.Structure):      # rtc_geometry
                 ("owner", C.c_void_p)]
 
 
+class Config(C.Structure):        # rtc_config
+    _fields_ = [("grid_resolution", c_uint3), ("num_threads", C.c_uint32),
+                ("num_samples", C.c_uint16), ("max_bounce", C.c_uint16)]
+
+
+class HostScene(C.Structure):     # rtc_host_scene
+    _fields_ = [("camera", Camera),
+                ("positions", C.POINTER(C.c_float)), ("tri_data", C.POINTER(TriData)),
+                ("num_tris", C.c_uint32),
+                ("materials", C.POINTER(Material)), ("num_materials", C.c_uint32),
+                ("num_images", C.c_uint32), ("owner", C.c_void_p)]
+
+
 # Every symbol include/rtc.h declares (checked by tests/test_abi.py against the built library).
 EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
     "rtc_resolve", "rtc_scene_stats", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_last_error", "rtc_abi_version", "rtc_device_count",
+    "rtc_config_load", "rtc_gltf_load", "rtc_host_scene_free", "rtc_png_write", "rtc_png_read",
 ]

@@ -52,6 +52,12 @@ def lib():
     L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
     L.rtc_geometry_free.argtypes = [C.POINTER(abi.Geometry)]
     L.rtc_geometry_free.restype = None
+    L.rtc_config_load.argtypes = [C.c_char_p, C.POINTER(abi.Config)]
+    L.rtc_gltf_load.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(abi.HostScene)]
+    L.rtc_host_scene_free.argtypes = [C.POINTER(abi.HostScene)]
+    L.rtc_host_scene_free.restype = None
+    L.rtc_png_write.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.rtc_png_read.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]
     if L.rtc_abi_version() != abi.RTC_ABI_VERSION and not os.environ.get("RTC_SKIP_ABI_CHECK"):
         raise ImportError("librtc.so ABI %d != binding ABI %d" % (L.rtc_abi_version(), abi.RTC_ABI_VERSION))
     _LIB = L
@@ -65,6 +71,64 @@ def _check(rc):
 
 def device_count():
     return int(lib().rtc_device_count())
+
+
+# ---- main.zig's file contracts + stage1 ---------------------------------------------------------------
+def load_config(path="config.json"):
+    """main.Config (src/main.zig:56-69). Returns dict(grid_resolution, num_threads|None, num_samples, max_bounce)."""
+    c = abi.Config()
+    _check(lib().rtc_config_load(os.fsencode(path), C.byref(c)))
+    return {"grid_resolution": tuple(int(x) for x in c.grid_resolution), "num_threads": int(c.num_threads) or None,
+            "num_samples": int(c.num_samples), "max_bounce": int(c.max_bounce)}
+
+
+class HostSceneData:
+    """What stage1 leaves in memory (src/main.zig:104-112), copied out of rtc_gltf_load into numpy:
+    camera (abi.Camera), positions [N,3,3], tri_data [N] (TRI_DATA_DTYPE), materials [MaterialData]."""
+
+    def __init__(self, path, camera=None, width=None, height=None, num_threads=1):
+        hs = abi.HostScene()
+        _check(lib().rtc_gltf_load(os.fsencode(path), camera.encode() if camera is not None else None,
+                                   int(width or 0), int(height or 0), int(num_threads), C.byref(hs)))
+        try:
+            n = int(hs.num_tris)
+            self.camera = abi.Camera.from_buffer_copy(hs.camera)
+            self.num_images = int(hs.num_images)
+            if n:
+                self.positions = np.ctypeslib.as_array(hs.positions, (n, 3, 3)).copy()
+                self.tri_data = np.ctypeslib.as_array(C.cast(hs.tri_data, C.POINTER(C.c_uint8)), (n * 68,)).copy().view(TRI_DATA_DTYPE)
+            else:
+                self.positions, self.tri_data = np.zeros((0, 3, 3), np.float32), np.zeros(0, TRI_DATA_DTYPE)
+            self.materials = []
+            for i in range(int(hs.num_materials)):
+                m = hs.materials[i]
+                tex = []
+                for t in (m.base_color, m.emissive, m.transparency):
+                    arr = np.ctypeslib.as_array(t.texels, (t.h, t.w, t.channels)).copy()
+                    td = TextureData(arr)
+                    td.u_min, td.u_max, td.v_min, td.v_max = t.u_min, t.u_max, t.v_min, t.v_max
+                    tex.append(td)
+                self.materials.append(MaterialData(*tex))
+        finally:
+            lib().rtc_host_scene_free(C.byref(hs))
+
+
+def png_write(path, rgb):
+    """stbi_write_png(path, w, h, 3, img, 3*w) (src/main.zig:130-135)."""
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    h, w, c = rgb.shape
+    if c != 3:
+        raise ValueError("rgb must be [h,w,3]")
+    _check(lib().rtc_png_write(os.fsencode(path), w, h, rgb.ctypes.data))
+
+
+def png_read(path):
+    w, h, p = C.c_uint32(), C.c_uint32(), C.c_void_p()
+    _check(lib().rtc_png_read(os.fsencode(path), C.byref(w), C.byref(h), C.byref(p)))
+    try:
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), (h.value, w.value, 3)).copy()
+    finally:
+        C.CDLL(None).free(p)
 
 
 # ---- stage2: Geometry.build + bakeInto ---------------------------------------------------------
