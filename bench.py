@@ -39,6 +39,10 @@ OVERRIDE = {}      # --spp / --height (profiling runs only; the default line use
 # dram__bytes_read.sum + dram__bytes_write.sum per k_trace launch from the committed `ncu --set full` capture
 # (profiles/); None until a capture of the current kernel exists.
 TRAFFIC = {}
+try:
+    TRAFFIC = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["per_launch_bytes"]
+except (OSError, KeyError, ValueError):
+    pass
 
 
 def build_workload(name):
@@ -174,6 +178,15 @@ def run_gpu(args, rank, world, local_rank):
     t0 = time.perf_counter()
     scene = rtc.Scene(geo, spec.materials, device=local_rank)
     upload_s = time.perf_counter() - t0
+    device_build = None
+    if rank == 0:
+        # the same scene built and baked ON the device from the triangle soup (not timed as part
+        # of a step; reported beside the host-thread build it replaces)
+        sb = rtc.Scene.from_soup(spec.positions, spec.tri_data, geo.grid.resolution, spec.materials, device=local_rank)
+        bi = sb.build_info
+        assert (int(bi.num_tris), int(bi.empty_cells)) == (geo.num_tris, geo.empty_cells), "device build disagrees with the host build"
+        device_build = {"kernels_ms": round(float(bi.device_ms), 3), "call_ms": round(float(bi.total_ms), 1)}
+        sb.close()
     P = cam.w * cam.h
     math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
     total = spp * world                             # weak scaling: the frame's sample count grows with N
@@ -274,6 +287,7 @@ def run_gpu(args, rank, world, local_rank):
         cfg = workload_config(args.workload, spec, geo, cam, spp, bounce, world)
         cfg["math"] = "exact (no FMA contraction)" if math == abi.RTC_MATH_EXACT else "fast (FMA contraction)"
         cfg["host_build_s"] = round(build_s, 3); cfg["scene_upload_s"] = round(upload_s, 3)
+        cfg["device_build"] = device_build
         cfg["per_ray"] = {"cells": round(cs["cells_visited"] / cs["rays"], 2), "tris": round(cs["tris_tested"] / cs["rays"], 2),
                           "bytes": round(algo_bytes / cs["rays"], 1), "rays_per_path": round(cs["rays"] / cs["paths"], 3)}
         out = {

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 4u
+#define RTC_ABI_VERSION 5u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -229,6 +229,33 @@ typedef struct rtc_geometry {
 int  rtc_geometry_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
                         const uint32_t grid_resolution[3], rtc_geometry* out);
 void rtc_geometry_free(rtc_geometry* g);
+
+/* The same producer on the GPU (sm_100a kernels: bounding box, per-triangle cell binning with the
+ * reference's triangle/box overlap test, scan, sort, bake). Outputs are bit-identical to
+ * rtc_geometry_build's and are freed with rtc_geometry_free. device < 0 = current device. */
+int  rtc_geometry_build_device(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
+                               const uint32_t grid_resolution[3], int device, rtc_geometry* out);
+
+/* What the device build reports (the reference logs the same figures, src/stage2.zig:97-100,126-128). */
+typedef struct rtc_build_info {
+    rtc_grid grid;
+    uint64_t num_cells;
+    uint64_t num_tris;       /* baked count */
+    uint32_t num_src_tris;
+    uint32_t empty_cells;
+    uint32_t min_tris, max_tris;
+    float    device_ms;      /* CUDA-event time of the build kernels (after the soup's H2D copy) */
+    double   total_ms;       /* wall time of the whole call: upload + build + bake + textures    */
+} rtc_build_info;
+
+/* geometry.build() + geometry.bakeInto(&scene) (src/main.zig:117-118) + rtc_scene_create in one step, with
+ * the grid built and baked ON the device: the soup is uploaded once and the baked arrays never exist on the
+ * host. The resulting scene renders bit-identically to rtc_scene_create(rtc_geometry_build(...)).
+ * info may be NULL. */
+int  rtc_scene_create_from_soup(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
+                                const uint32_t grid_resolution[3],
+                                const rtc_material* materials, uint32_t num_materials,
+                                int device, rtc_scene** out, rtc_build_info* info);
 
 /* ---- stage1 + main.zig's file contracts as the path's callers ---------
  * Host-only (no GPU needed). These are what a host that is NOT the Zig program uses to honour the

@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 4
+RTC_ABI_VERSION = 5
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -107,6 +107,13 @@ class Geometry(C.Structure):      # rtc_geometry
                 ("owner", C.c_void_p)]
 
 
+class BuildInfo(C.Structure):     # rtc_build_info
+    _fields_ = [("grid", Grid), ("num_cells", C.c_uint64), ("num_tris", C.c_uint64),
+                ("num_src_tris", C.c_uint32), ("empty_cells", C.c_uint32),
+                ("min_tris", C.c_uint32), ("max_tris", C.c_uint32),
+                ("device_ms", C.c_float), ("total_ms", C.c_double)]
+
+
 class Config(C.Structure):        # rtc_config
     _fields_ = [("grid_resolution", c_uint3), ("num_threads", C.c_uint32),
                 ("num_samples", C.c_uint16), ("max_bounce", C.c_uint16)]
@@ -124,6 +131,7 @@ class HostScene(C.Structure):     # rtc_host_scene
 EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
     "rtc_resolve", "rtc_scene_stats", "rtc_geometry_build", "rtc_geometry_free",
+    "rtc_geometry_build_device", "rtc_scene_create_from_soup",
     "rtc_last_error", "rtc_abi_version", "rtc_device_count",
     "rtc_config_load", "rtc_gltf_load", "rtc_host_scene_free", "rtc_png_write", "rtc_png_read",
 ]

@@ -1,10 +1,7 @@
 // rtc_api.cu — the C ABI of include/rtc.h over the sm_100a kernels in rtc_kernels.cu.
 // Replaces `scene.render(threads, camera, img)` (src/main.zig:126, src/stage3.zig:247).
 // No CPU fallback: every compute entry point fails with RTC_ERR_NO_DEVICE without an sm_100 GPU.
-#include "../../include/rtc.h"
-#include "rtc_kernels.h"
-
-#include <cuda_runtime.h>
+#include "rtc_internal.h"
 
 #include <cstdarg>
 #include <cstdio>
@@ -15,10 +12,10 @@
 #include <vector>
 
 namespace {
-
 thread_local std::string g_error;
+}  // namespace
 
-int fail(int code, const char* fmt, ...)
+int rtc_fail_(int code, const char* fmt, ...)
 {
     char buf[512];
     va_list ap;
@@ -28,21 +25,14 @@ int fail(int code, const char* fmt, ...)
     g_error = buf;
     return code;
 }
-
-}  // namespace
+#define fail rtc_fail_
 
 // used by rtc_geometry.cpp
 int rtc_set_error_(int code, const char* msg) { g_error = msg; return code; }
 
 namespace {
 
-#define CU(call)                                                                                  \
-    do {                                                                                          \
-        cudaError_t e_ = (call);                                                                  \
-        if (e_ != cudaSuccess)                                                                    \
-            return fail(e_ == cudaErrorMemoryAllocation ? RTC_ERR_OUT_OF_MEMORY : RTC_ERR_CUDA,   \
-                        "%s: %s", #call, cudaGetErrorString(e_));                                 \
-    } while (0)
+#define CU(call) RTC_CU(call)
 
 float __uint_as_float_host(uint32_t u) { float f; memcpy(&f, &u, sizeof f); return f; }
 
@@ -53,55 +43,9 @@ bool device_is_sm100(int dev)
     return p.major == 10;
 }
 
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (dev != prev) cudaSetDevice(dev); }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
+using DeviceGuard = RtcDeviceGuard;
 
 }  // namespace
-
-// Device-resident scene + per-scene scratch reused across rtc_render calls.
-struct rtc_scene {
-    int device = 0;
-    int sm_count = 0;
-    rtc::DevScene dev{};
-    std::vector<void*> allocs;          // everything cudaMalloc'ed for the scene
-    unsigned long long* counters = nullptr;
-    uint32_t* work = nullptr;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    // frame scratch (grown on demand)
-    uint32_t cap_pixels = 0;
-    float4* accum = nullptr;
-    uint8_t* d_rgb = nullptr;
-    float* d_radiance = nullptr;
-    uint32_t* d_hit_id = nullptr;
-    float* d_hit_tuv = nullptr;
-    uint8_t* h_pinned = nullptr;        // staging for the D2H copies (rgb | radiance | hit_id | tuv)
-    size_t h_pinned_bytes = 0;
-    uint64_t num_tris = 0;
-    uint32_t num_src_tris = 0;
-    // wavefront scratch (grown on demand) + kernels launched since the counters were last read
-    rtc::WaveScratch wave{};
-    std::vector<void*> wave_allocs;
-    bool wave_budget_limited = false;
-    uint64_t launches = 0;
-    std::vector<cudaEvent_t> timer_events;
-    rtc::TraceTimer timer{};
-
-    template <typename T>
-    int alloc(T** out, size_t count)
-    {
-        void* p = nullptr;
-        cudaError_t e = cudaMalloc(&p, count ? count * sizeof(T) : sizeof(T));
-        if (e != cudaSuccess)
-            return fail(RTC_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes): %s", count * sizeof(T), cudaGetErrorString(e));
-        allocs.push_back(p);
-        *out = static_cast<T*>(p);
-        return RTC_OK;
-    }
-};
 
 extern "C" {
 
@@ -168,11 +112,9 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
             return fail(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)",
                         g.resolution[a], a, rtc::kMaxGridRes);
     // validate cells; re-lay them out by packed cell (rtc_device.cuh) and derive the two occupancy levels
-    const uint32_t nbx = (g.resolution[0] + 3) / 4, nby = (g.resolution[1] + 3) / 4, nbz = (g.resolution[2] + 3) / 4;
-    auto clog2 = [](uint32_t n) { uint32_t l = 0; while ((1u << l) < n) ++l; return l; };
-    const uint32_t lx = clog2(nbx), ly = clog2(nby), lz = clog2(nbz);
-    uint32_t shift[3] = { 6u, 6u + lx, 6u + lx + ly };
-    const size_t nb = (size_t)1 << (lx + ly + lz);
+    rtc::DevScene& d = s->dev;
+    const size_t nb = rtc_scene_set_packing_(d, g.resolution);
+    const uint32_t* shift = d.shift;
     std::vector<rtc_cell> cells_b(nb * 64, rtc_cell{ 0u, 0u });
     std::vector<unsigned long long> fine(nb, 0ull);
     std::vector<uint32_t> coarse((nb + 31) / 32, 0u);
@@ -202,7 +144,6 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     if (num_src == 0) num_src = desc->num_tris ? max_src + 1 : 0;
     if (desc->num_tris && max_src >= num_src) return fail(RTC_ERR_INVALID_ARGUMENT, "src_tri %u >= num_src_tris %u", max_src, num_src);
 
-    rtc::DevScene& d = s->dev;
     for (int i = 0; i < 3; ++i) {
         d.bmin[i] = g.bbox_min[i]; d.bmax[i] = g.bbox_max[i];
         d.res[i] = g.resolution[i]; d.cell[i] = g.cell_size[i];
@@ -240,26 +181,51 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
         CU(cudaMemcpy(d_pos, pos.data(), pos.size() * sizeof(float4), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(d_data, data.data(), data.size() * sizeof(float4), cudaMemcpyHostToDevice));
     }
-    std::vector<rtc::DevMaterial> mats(desc->num_materials);
+    if (int rc = rtc_scene_upload_materials_(s, desc->materials, desc->num_materials)) return rc;
+    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.coarse_words = (uint32_t)coarse.size();
+    d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data;
+    s->num_tris = desc->num_tris;
+    s->num_src_tris = num_src;
+
+    return rtc_scene_finish_(s);
+}
+
+}  // namespace
+
+size_t rtc_scene_set_packing_(rtc::DevScene& d, const uint32_t res[3])
+{
+    const uint32_t nbx = (res[0] + 3) / 4, nby = (res[1] + 3) / 4, nbz = (res[2] + 3) / 4;
+    auto clog2 = [](uint32_t n) { uint32_t l = 0; while ((1u << l) < n) ++l; return l; };
+    const uint32_t lx = clog2(nbx), ly = clog2(nby), lz = clog2(nbz);
+    d.shift[0] = 6u; d.shift[1] = 6u + lx; d.shift[2] = 6u + lx + ly;
+    d.mask[0] = 0x03u | (((1u << lx) - 1u) << d.shift[0]);
+    d.mask[1] = 0x0Cu | (((1u << ly) - 1u) << d.shift[1]);
+    d.mask[2] = 0x30u | (((1u << lz) - 1u) << d.shift[2]);
+    const size_t nb = (size_t)1 << (lx + ly + lz);
+    d.coarse_words = (uint32_t)((nb + 31) / 32);
+    return nb;
+}
+
+int rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uint32_t num_materials)
+{
+    if (!materials || num_materials == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "scene has no materials");
+    std::vector<rtc::DevMaterial> mats(num_materials);
     std::vector<std::pair<const float*, void*>> seen;
-    for (uint32_t m = 0; m < desc->num_materials; ++m) {
-        if (int rc = upload_texture(s, desc->materials[m].base_color, 3, &mats[m].base, seen)) return rc;
-        if (int rc = upload_texture(s, desc->materials[m].emissive, 3, &mats[m].emissive, seen)) return rc;
-        if (int rc = upload_texture(s, desc->materials[m].transparency, 1, &mats[m].alpha, seen)) return rc;
+    for (uint32_t m = 0; m < num_materials; ++m) {
+        if (int rc = upload_texture(s, materials[m].base_color, 3, &mats[m].base, seen)) return rc;
+        if (int rc = upload_texture(s, materials[m].emissive, 3, &mats[m].emissive, seen)) return rc;
+        if (int rc = upload_texture(s, materials[m].transparency, 1, &mats[m].alpha, seen)) return rc;
     }
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;
     CU(cudaMemcpy(d_mats, mats.data(), mats.size() * sizeof(rtc::DevMaterial), cudaMemcpyHostToDevice));
-    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse; d.coarse_words = (uint32_t)coarse.size();
-    d.mask[0] = 0x03u | (((1u << lx) - 1u) << shift[0]);
-    d.mask[1] = 0x0Cu | (((1u << ly) - 1u) << shift[1]);
-    d.mask[2] = 0x30u | (((1u << lz) - 1u) << shift[2]);
-    for (int a = 0; a < 3; ++a) d.shift[a] = shift[a];
-    d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = d_data; d.materials = d_mats;
-    d.num_materials = desc->num_materials;
-    s->num_tris = desc->num_tris;
-    s->num_src_tris = num_src;
+    s->dev.materials = d_mats;
+    s->dev.num_materials = num_materials;
+    return RTC_OK;
+}
 
+int rtc_scene_finish_(rtc_scene* s)
+{
     if (int rc = s->alloc(&s->counters, (size_t)rtc::CNT_N)) return rc;
     if (int rc = s->alloc(&s->work, (size_t)4)) return rc;
     CU(cudaMemset(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long)));
@@ -272,7 +238,7 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     return RTC_OK;
 }
 
-void scene_free(rtc_scene* s)
+void rtc_scene_free_(rtc_scene* s)
 {
     if (!s) return;
     DeviceGuard guard(s->device);
@@ -288,13 +254,8 @@ void scene_free(rtc_scene* s)
     delete s;
 }
 
-}  // namespace
-
-extern "C" {
-
-int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out)
+int rtc_scene_new_(int device, rtc_scene** out)
 {
-    if (!desc || !out) return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_create: null argument");
     *out = nullptr;
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return fail(RTC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)"); }
@@ -304,17 +265,36 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out)
     rtc_scene* s = new (std::nothrow) rtc_scene();
     if (!s) return fail(RTC_ERR_OUT_OF_MEMORY, "host allocation failed");
     s->device = device;
-    DeviceGuard guard(device);
+    RtcDeviceGuard guard(device);
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device);
     s->sm_count = prop.multiProcessorCount;
-    const int rc = scene_upload(s, desc);
-    if (rc != RTC_OK) { const std::string keep = g_error; scene_free(s); g_error = keep; return rc; }
     *out = s;
     return RTC_OK;
 }
 
-void rtc_scene_destroy(rtc_scene* scene) { scene_free(scene); }
+void rtc_keep_error_free_(rtc_scene* s)
+{
+    const std::string keep = g_error;
+    rtc_scene_free_(s);
+    g_error = keep;
+}
+
+extern "C" {
+
+int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out)
+{
+    if (!desc || !out) return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_create: null argument");
+    rtc_scene* s = nullptr;
+    if (int rc = rtc_scene_new_(device, &s)) return rc;
+    DeviceGuard guard(s->device);
+    const int rc = scene_upload(s, desc);
+    if (rc != RTC_OK) { rtc_keep_error_free_(s); return rc; }
+    *out = s;
+    return RTC_OK;
+}
+
+void rtc_scene_destroy(rtc_scene* scene) { rtc_scene_free_(scene); }
 
 }  // extern "C"
 

@@ -1,0 +1,558 @@
+// rtc_build.cu — Geometry.build + bakeInto (src/stage2.zig:44-164) on the device, from a triangle soup that
+// was uploaded once. SURVEY §8(f) #1: the step immediately before the render path, which the reference runs
+// serially on one host thread.
+//
+//   k_bbox      initGrid (stage2.zig:44-57): min/max over all vertices            -> Grid.init (linalg.zig:412-418)
+//   k_bin       initCells / initIndices (stage2.zig:59-81, 104-125): per triangle, the cells of its bounding
+//               range that pass intersectsTriangleAabb (linalg.zig:500-563). COUNT adds to the cell's counter,
+//               EMIT appends the key (cell << 32 | triangle). Triangles whose range exceeds kInlineCells
+//               are deferred to k_bin_big, one CTA per triangle.
+//   scan        exclusive sum of the counters = Cell.begin (stage2.zig:82-96)      (cub::DeviceScan)
+//   sort        the keys, ascending: cell-major, source-triangle order inside the cell — the order the
+//               reference's serial scatter produces and Scene.traceRay's tie-break depends on (cub::DeviceRadixSort)
+//   k_cells     Cell{begin,end} in the reference's x-fastest order + the empty/min/max statistics (stage2.zig:76-100)
+//   k_layout    the same cells by packed index + the two occupancy levels (rtc_device.cuh)
+//   k_bake_soa  bakeInto (stage2.zig:137-164) + Triangle.init (linalg.zig:688-694) into the SoA float4 arrays
+//   k_pack_data Triangle.Data per SOURCE triangle in the 5-float4 layout k_shade reads
+//   k_bake_aos  the same bake in the C ABI's AoS layout, for rtc_geometry_build_device (parity with the host build)
+//
+// Compiled with -fmad=false, IEEE div/sqrt: the overlap test decides which cells hold a triangle and must
+// evaluate exactly like the reference's fp32 code. CUB (scan, radix sort) is library plumbing of the build
+// step, not part of the render path.
+#include "rtc_internal.h"
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <new>
+
+namespace rtc {
+namespace build {
+
+static constexpr int kThreads = 256;
+static constexpr uint32_t kInlineCells = 64;       // ranges up to this many cells are tested by the triangle's own thread
+
+struct GridP {
+    float bmin[3], cell[3];
+    uint32_t res[3];
+};
+
+// ---- initGrid: order-independent min/max through the monotone float -> int map (-0 < +0) ----
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7FFFFFFF; }
+__host__ __device__ __forceinline__ float ord2f_bits(int i, bool)
+{
+    const int b = i >= 0 ? i : i ^ 0x7FFFFFFF;
+    float f;
+    memcpy(&f, &b, sizeof f);
+    return f;
+}
+
+__global__ void __launch_bounds__(kThreads) k_bbox(const float* __restrict__ pos, uint64_t num_vertices, int* __restrict__ out /* min xyz, max xyz */)
+{
+    int lo[3] = { 0x7F800000, 0x7F800000, 0x7F800000 };                 // +inf
+    int hi[3] = { (int)0x807FFFFF, (int)0x807FFFFF, (int)0x807FFFFF };  // ord(-inf)
+    for (uint64_t v = (uint64_t)blockIdx.x * kThreads + threadIdx.x; v < num_vertices; v += (uint64_t)gridDim.x * kThreads) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float p = __ldg(pos + 3 * v + a);
+            if (p != p) continue;                                       // @min/@max skip NaN (fminf/fmaxf)
+            const int o = f2ord(p);
+            lo[a] = min(lo[a], o); hi[a] = max(hi[a], o);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = __reduce_min_sync(0xFFFFFFFFu, lo[a]);
+        hi[a] = __reduce_max_sync(0xFFFFFFFFu, hi[a]);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { atomicMin(out + a, lo[a]); atomicMax(out + 3 + a, hi[a]); }
+    }
+}
+
+// ---- intersectsTriangleAabbSat / intersectsTriangleAabb (src/linalg.zig:500-563), expression for expression
+// like the host build (rtc_geometry.cpp) and the oracle ----
+__device__ __forceinline__ bool sat(v3 a, v3 b, v3 c, v3 e, v3 axis)
+{
+    const float p0 = dot(a, axis), p1 = dot(b, axis), p2 = dot(c, axis);
+    const float r = e.x * fabsf(dot(mk(1.0f, 0.0f, 0.0f), axis)) + e.y * fabsf(dot(mk(0.0f, 1.0f, 0.0f), axis)) +
+                    e.z * fabsf(dot(mk(0.0f, 0.0f, 1.0f), axis));
+    const float hi = fmaxf(p0, fmaxf(p1, p2)), lo = fminf(p0, fminf(p1, p2));
+    return !(fmaxf(-hi, lo) > r);
+}
+
+__device__ __forceinline__ bool tri_box(v3 t0, v3 t1, v3 t2, v3 bmin, v3 bmax)
+{
+    const v3 center = scale(bmax + bmin, 0.5f), e = scale(bmax - bmin, 0.5f);
+    const v3 a = t0 - center, b = t1 - center, c = t2 - center;
+    struct { v3 ab, bc, ca, n; } x;
+    x.ab = normalize(b - a); x.bc = normalize(c - b); x.ca = normalize(a - c);
+    x.n = cross(x.ab, x.bc);
+    if (!sat(a, b, c, e, mk(0.0f, -x.ab.z, x.ab.y))) return false;
+    if (!sat(a, b, c, e, mk(0.0f, -x.bc.z, x.bc.y))) return false;
+    if (!sat(a, b, c, e, mk(0.0f, -x.ca.z, x.ca.y))) return false;
+    if (!sat(a, b, c, e, mk(x.ab.z, 0.0f, -x.ab.x))) return false;
+    if (!sat(a, b, c, e, mk(x.bc.z, 0.0f, -x.bc.x))) return false;
+    if (!sat(a, b, c, e, mk(x.ca.z, 0.0f, -x.ca.x))) return false;
+    if (!sat(a, b, c, e, mk(-x.ab.y, x.ab.x, 0.0f))) return false;
+    if (!sat(a, b, c, e, mk(-x.bc.y, x.bc.x, 0.0f))) return false;
+    if (!sat(a, b, c, e, mk(-x.ca.y, x.ca.x, 0.0f))) return false;
+    if (!sat(a, b, c, e, mk(1.0f, 0.0f, 0.0f))) return false;
+    if (!sat(a, b, c, e, mk(0.0f, 1.0f, 0.0f))) return false;
+    if (!sat(a, b, c, e, mk(0.0f, 0.0f, 1.0f))) return false;
+    return sat(a, b, c, e, x.n);
+}
+
+struct Tri { v3 p0, p1, p2; };
+__device__ __forceinline__ Tri load_tri(const float* __restrict__ pos, uint32_t t)
+{
+    const float* p = pos + 9 * (size_t)t;
+    Tri r;
+    r.p0 = mk(__ldg(p), __ldg(p + 1), __ldg(p + 2));
+    r.p1 = mk(__ldg(p + 3), __ldg(p + 4), __ldg(p + 5));
+    r.p2 = mk(__ldg(p + 6), __ldg(p + 7), __ldg(p + 8));
+    return r;
+}
+// Grid.getCellIdx (src/linalg.zig:424-427)
+__device__ __forceinline__ void cell_idx(const GridP& g, v3 p, uint32_t out[3])
+{
+    out[0] = min(f2u((p.x - g.bmin[0]) / g.cell[0]), g.res[0] - 1u);
+    out[1] = min(f2u((p.y - g.bmin[1]) / g.cell[1]), g.res[1] - 1u);
+    out[2] = min(f2u((p.z - g.bmin[2]) / g.cell[2]), g.res[2] - 1u);
+}
+__device__ __forceinline__ void tri_range(const GridP& g, const Tri& t, uint32_t lo[3], uint32_t hi[3])
+{
+    const v3 mn = mk(fminf(t.p0.x, fminf(t.p1.x, t.p2.x)), fminf(t.p0.y, fminf(t.p1.y, t.p2.y)), fminf(t.p0.z, fminf(t.p1.z, t.p2.z)));
+    const v3 mx = mk(fmaxf(t.p0.x, fmaxf(t.p1.x, t.p2.x)), fmaxf(t.p0.y, fmaxf(t.p1.y, t.p2.y)), fmaxf(t.p0.z, fmaxf(t.p1.z, t.p2.z)));
+    cell_idx(g, mn, lo);
+    cell_idx(g, mx, hi);
+}
+// Grid.getCellBbox (src/linalg.zig:433-441) + the overlap test for one cell of the range
+__device__ __forceinline__ bool cell_overlaps(const GridP& g, const Tri& t, uint32_t x, uint32_t y, uint32_t z)
+{
+    const v3 bmin = mk(g.bmin[0] + g.cell[0] * (float)x, g.bmin[1] + g.cell[1] * (float)y, g.bmin[2] + g.cell[2] * (float)z);
+    const v3 bmax = bmin + mk(g.cell[0], g.cell[1], g.cell[2]);
+    return tri_box(t.p0, t.p1, t.p2, bmin, bmax);
+}
+
+struct BinOut {
+    uint32_t* count;                    // per cell (COUNT)
+    unsigned long long* keys;           // EMIT: cell << 32 | triangle
+    unsigned long long* cursor;         // [0] keys written (EMIT) / pairs counted (COUNT), [1] deferred triangles
+    uint32_t* big;                      // deferred triangle ids
+};
+
+template <bool EMIT>
+__device__ __forceinline__ void visit(const BinOut& o, uint32_t cell, uint32_t tri)
+{
+    if (EMIT) {
+        // one atomic per converged group of lanes, order inside the group is irrelevant (the keys get sorted)
+        const uint32_t m = __activemask();
+        const uint32_t lane = threadIdx.x & 31u;
+        const int leader = __ffs(m) - 1;
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomicAdd(o.cursor, (unsigned long long)__popc(m));
+        base = __shfl_sync(m, base, leader);
+        o.keys[base + __popc(m & ((1u << lane) - 1u))] = ((unsigned long long)cell << 32) | tri;
+    } else {
+        atomicAdd(o.count + cell, 1u);
+    }
+}
+
+template <bool EMIT>
+__global__ void __launch_bounds__(kThreads) k_bin(const float* __restrict__ pos, uint32_t num_tris, const __grid_constant__ GridP g, BinOut o)
+{
+    const uint32_t t = blockIdx.x * kThreads + threadIdx.x;
+    uint32_t mine = 0;
+    if (t < num_tris) {
+        const Tri tri = load_tri(pos, t);
+        uint32_t lo[3], hi[3];
+        tri_range(g, tri, lo, hi);
+        const uint64_t n = (uint64_t)(hi[0] - lo[0] + 1u) * (hi[1] - lo[1] + 1u) * (hi[2] - lo[2] + 1u);
+        if (n > kInlineCells) {
+            o.big[atomicAdd(o.cursor + 1, 1ull)] = t;
+        } else {
+            for (uint32_t z = lo[2]; z <= hi[2]; ++z)
+                for (uint32_t y = lo[1]; y <= hi[1]; ++y)
+                    for (uint32_t x = lo[0]; x <= hi[0]; ++x)
+                        if (cell_overlaps(g, tri, x, y, z)) { visit<EMIT>(o, (z * g.res[1] + y) * g.res[0] + x, t); mine += 1; }
+        }
+    }
+    if (!EMIT) {
+        mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(o.cursor, (unsigned long long)mine);
+    }
+}
+
+// Deferred triangles (walls, floors: ranges of thousands of cells): one CTA per triangle, lanes stride the range.
+template <bool EMIT>
+__global__ void __launch_bounds__(kThreads) k_bin_big(const float* __restrict__ pos, const __grid_constant__ GridP g, BinOut o)
+{
+    const uint32_t nbig = (uint32_t)o.cursor[1];
+    uint32_t mine = 0;
+    for (uint32_t b = blockIdx.x; b < nbig; b += gridDim.x) {
+        const uint32_t t = o.big[b];
+        const Tri tri = load_tri(pos, t);
+        uint32_t lo[3], hi[3];
+        tri_range(g, tri, lo, hi);
+        const uint32_t nx = hi[0] - lo[0] + 1u, ny = hi[1] - lo[1] + 1u, nz = hi[2] - lo[2] + 1u;
+        const uint64_t n = (uint64_t)nx * ny * nz;
+        for (uint64_t i = threadIdx.x; i < n; i += kThreads) {
+            const uint32_t x = lo[0] + (uint32_t)(i % nx), y = lo[1] + (uint32_t)((i / nx) % ny), z = lo[2] + (uint32_t)(i / ((uint64_t)nx * ny));
+            if (cell_overlaps(g, tri, x, y, z)) { visit<EMIT>(o, (z * g.res[1] + y) * g.res[0] + x, t); mine += 1; }
+        }
+    }
+    if (!EMIT) {
+        mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(o.cursor, (unsigned long long)mine);
+    }
+}
+
+// Cell{begin,end} (x-fastest order) + stage2's statistics: stats = {empty cells, min, max over non-empty cells}
+__global__ void __launch_bounds__(kThreads) k_cells(const uint32_t* __restrict__ count, const uint32_t* __restrict__ begin, uint32_t num_cells,
+                                                    uint2* __restrict__ cells, uint32_t* __restrict__ stats)
+{
+    const uint32_t c = blockIdx.x * kThreads + threadIdx.x;
+    uint32_t n = 0;
+    const bool on = c < num_cells;
+    if (on) { n = count[c]; const uint32_t b = begin[c]; cells[c] = make_uint2(b, b + n); }
+    const uint32_t empty = __popc(__ballot_sync(0xFFFFFFFFu, on && n == 0u));
+    const uint32_t mn = __reduce_min_sync(0xFFFFFFFFu, on && n ? n : 0xFFFFFFFFu);
+    const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, on ? n : 0u);
+    if ((threadIdx.x & 31) == 0) {
+        if (empty) atomicAdd(stats, empty);
+        if (mn != 0xFFFFFFFFu) atomicMin(stats + 1, mn);
+        if (mx) atomicMax(stats + 2, mx);
+    }
+}
+
+// The cells by packed index (rtc_device.cuh) and the two occupancy levels. cells_b / fine / coarse are zeroed before.
+struct Packing { uint32_t shift[3]; };
+__global__ void __launch_bounds__(kThreads) k_layout(const uint2* __restrict__ cells, const __grid_constant__ GridP g, const __grid_constant__ Packing pk,
+                                                     uint2* __restrict__ cells_b, unsigned long long* __restrict__ fine, uint32_t* __restrict__ coarse)
+{
+    const uint32_t c = blockIdx.x * kThreads + threadIdx.x;
+    const uint32_t num_cells = g.res[0] * g.res[1] * g.res[2];
+    if (c >= num_cells) return;
+    const uint32_t x = c % g.res[0], y = (c / g.res[0]) % g.res[1], z = c / (g.res[0] * g.res[1]);
+    const uint2 cell = cells[c];
+    const uint32_t pc = pack_cell(pk.shift, x, y, z);
+    cells_b[pc] = cell;
+    if (cell.y > cell.x) {
+        const uint32_t bi = pc >> 6;
+        atomicOr(fine + bi, 1ull << (pc & 63u));
+        atomicOr(coarse + (bi >> 5), 1u << (bi & 31u));
+    }
+}
+
+// bakeInto (src/stage2.zig:137-164): duplicate the triangles in cell order; Triangle.init (src/linalg.zig:688-694):
+// {v0, e1 = v1 - v0, e2 = v2 - v0}. v0.w carries the source-triangle id.
+__global__ void __launch_bounds__(kThreads) k_bake_soa(const unsigned long long* __restrict__ keys, uint64_t num_baked, const float* __restrict__ pos,
+                                                       float4* __restrict__ v0, float4* __restrict__ e1, float4* __restrict__ e2)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= num_baked) return;
+    const uint32_t s = (uint32_t)keys[i];
+    const Tri t = load_tri(pos, s);
+    const v3 a = t.p1 - t.p0, b = t.p2 - t.p0;
+    v0[i] = make_float4(t.p0.x, t.p0.y, t.p0.z, __uint_as_float(s));
+    e1[i] = make_float4(a.x, a.y, a.z, 0.0f);
+    e2[i] = make_float4(b.x, b.y, b.z, 0.0f);
+}
+
+// rtc_tri_data (17 words, AoS) -> 5 float4 per source triangle: 9 normal + 6 uv + material + src_tri + 3 pad.
+// flag[0] is set when a material index is out of range.
+__global__ void __launch_bounds__(kThreads) k_pack_data(const uint32_t* __restrict__ data, uint32_t num_tris, uint32_t num_materials,
+                                                        uint32_t* __restrict__ out, uint32_t* __restrict__ flag)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= (uint64_t)num_tris * 20u) return;
+    const uint32_t t = (uint32_t)(i / 20u), w = (uint32_t)(i % 20u);
+    uint32_t v = 0u;
+    if (w < 16u) v = data[17 * (size_t)t + w];
+    else if (w == 16u) v = t;
+    if (w == 15u && v >= num_materials) atomicOr(flag, 1u);
+    out[i] = v;
+}
+
+// The bake in the C ABI's layout: rtc_tri_pos (12 floats) and rtc_tri_data (17 words, src_tri = source index).
+__global__ void __launch_bounds__(kThreads) k_bake_aos(const unsigned long long* __restrict__ keys, uint64_t num_baked, const float* __restrict__ pos,
+                                                       const uint32_t* __restrict__ data, float4* __restrict__ tri_pos, uint32_t* __restrict__ tri_data)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= num_baked) return;
+    const uint32_t s = (uint32_t)keys[i];
+    const Tri t = load_tri(pos, s);
+    const v3 a = t.p1 - t.p0, b = t.p2 - t.p0;
+    tri_pos[3 * i] = make_float4(t.p0.x, t.p0.y, t.p0.z, 0.0f);
+    tri_pos[3 * i + 1] = make_float4(a.x, a.y, a.z, 0.0f);
+    tri_pos[3 * i + 2] = make_float4(b.x, b.y, b.z, 0.0f);
+    for (int w = 0; w < 16; ++w) tri_data[17 * i + w] = data[17 * (size_t)s + w];
+    tri_data[17 * i + 16] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Host side of the build. Everything is allocated with cudaMalloc and owned by `Built` until released.
+struct Built {
+    rtc_grid grid{};
+    float* d_pos = nullptr;             // the soup (9 floats / triangle)
+    uint32_t* d_data = nullptr;         // rtc_tri_data records (17 words / triangle)
+    uint2* d_cells = nullptr;           // num_cells, x-fastest
+    unsigned long long* d_keys = nullptr;   // num_baked sorted keys
+    uint32_t num_src = 0;
+    uint64_t num_cells = 0, num_baked = 0;
+    uint32_t empty_cells = 0, min_tris = 0, max_tris = 0;
+    float device_ms = 0.0f;
+    std::vector<void*> tmp;             // scratch freed at the end of the build
+    ~Built()
+    {
+        for (void* p : tmp) cudaFree(p);
+        cudaFree(d_pos); cudaFree(d_data); cudaFree(d_cells); cudaFree(d_keys);
+    }
+};
+
+template <typename T>
+static int dalloc(T** out, size_t count, std::vector<void*>* track)
+{
+    void* p = nullptr;
+    const cudaError_t e = cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+    if (e != cudaSuccess) return rtc_fail_(RTC_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes) in the grid build: %s", count * sizeof(T), cudaGetErrorString(e));
+    if (track) track->push_back(p);
+    *out = static_cast<T*>(p);
+    return RTC_OK;
+}
+
+static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris, const uint32_t res[3], cudaStream_t st, Built* b)
+{
+    static_assert(sizeof(rtc_tri_data) == 17 * sizeof(uint32_t), "rtc_tri_data is 17 words");
+    const uint64_t num_cells = (uint64_t)res[0] * res[1] * res[2];
+    if (num_cells >= ((uint64_t)1 << 32)) return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid has 2^32 cells or more");
+    b->num_cells = num_cells; b->num_src = num_tris;
+    cudaEvent_t e0, e1;
+    RTC_CU(cudaEventCreate(&e0));
+    RTC_CU(cudaEventCreate(&e1));
+    struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ e0, e1 };
+
+    if (int rc = dalloc(&b->d_pos, (size_t)num_tris * 9, nullptr)) return rc;
+    if (int rc = dalloc(&b->d_data, (size_t)num_tris * 17, nullptr)) return rc;
+    if (int rc = dalloc(&b->d_cells, (size_t)num_cells, nullptr)) return rc;
+    RTC_CU(cudaMemcpyAsync(b->d_pos, positions, (size_t)num_tris * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
+    RTC_CU(cudaMemcpyAsync(b->d_data, data, (size_t)num_tris * sizeof(rtc_tri_data), cudaMemcpyHostToDevice, st));
+    RTC_CU(cudaEventRecord(e0, st));
+
+    // initGrid
+    int* d_box = nullptr;
+    if (int rc = dalloc(&d_box, 6, &b->tmp)) return rc;
+    const int box_init[6] = { 0x7F800000, 0x7F800000, 0x7F800000, (int)0x807FFFFF, (int)0x807FFFFF, (int)0x807FFFFF };
+    RTC_CU(cudaMemcpyAsync(d_box, box_init, sizeof box_init, cudaMemcpyHostToDevice, st));
+    const uint64_t nv = (uint64_t)num_tris * 3;
+    if (nv) {
+        const unsigned gridx = (unsigned)std::min<uint64_t>((nv + kThreads - 1) / kThreads, 148u * 8u);
+        k_bbox<<<gridx, kThreads, 0, st>>>(b->d_pos, nv, d_box);
+    }
+    int box[6];
+    RTC_CU(cudaMemcpyAsync(box, d_box, sizeof box, cudaMemcpyDeviceToHost, st));
+    RTC_CU(cudaStreamSynchronize(st));
+    GridP g;
+    for (int a = 0; a < 3; ++a) {
+        const float lo = ord2f_bits(box[a], true), hi = ord2f_bits(box[3 + a], true);
+        b->grid.bbox_min[a] = lo; b->grid.bbox_max[a] = hi; b->grid.resolution[a] = res[a];
+        b->grid.cell_size[a] = (hi - lo) / (float)res[a];            // Grid.init (linalg.zig:412-418)
+        g.bmin[a] = lo; g.cell[a] = b->grid.cell_size[a]; g.res[a] = res[a];
+    }
+
+    // initCells: count
+    uint32_t* d_count = nullptr; uint32_t* d_begin = nullptr; unsigned long long* d_cursor = nullptr; uint32_t* d_big = nullptr; uint32_t* d_stats = nullptr;
+    if (int rc = dalloc(&d_count, (size_t)num_cells, &b->tmp)) return rc;
+    if (int rc = dalloc(&d_begin, (size_t)num_cells, &b->tmp)) return rc;
+    if (int rc = dalloc(&d_cursor, 2, &b->tmp)) return rc;
+    if (int rc = dalloc(&d_big, (size_t)num_tris, &b->tmp)) return rc;
+    if (int rc = dalloc(&d_stats, 3, &b->tmp)) return rc;
+    RTC_CU(cudaMemsetAsync(d_count, 0, (size_t)num_cells * sizeof(uint32_t), st));
+    RTC_CU(cudaMemsetAsync(d_cursor, 0, 2 * sizeof(unsigned long long), st));
+    BinOut o; o.count = d_count; o.keys = nullptr; o.cursor = d_cursor; o.big = d_big;
+    const unsigned tri_blocks = (num_tris + kThreads - 1) / kThreads;
+    if (num_tris) {
+        k_bin<false><<<tri_blocks, kThreads, 0, st>>>(b->d_pos, num_tris, g, o);
+        k_bin_big<false><<<148 * 8, kThreads, 0, st>>>(b->d_pos, g, o);
+    }
+    unsigned long long h_cursor[2] = { 0, 0 };
+    RTC_CU(cudaMemcpyAsync(h_cursor, d_cursor, sizeof h_cursor, cudaMemcpyDeviceToHost, st));
+    RTC_CU(cudaStreamSynchronize(st));
+    const uint64_t M = h_cursor[0];
+    if (M >= ((uint64_t)1 << 32)) return rtc_fail_(RTC_ERR_UNSUPPORTED, "more than 2^32 baked triangles");
+    b->num_baked = M;
+
+    // exclusive scan -> Cell.begin; cells + statistics
+    size_t scan_bytes = 0, sort_bytes = 0;
+    RTC_CU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, d_count, d_begin, (int)num_cells, st));
+    unsigned long long* d_keys_in = nullptr;
+    if (int rc = dalloc(&d_keys_in, (size_t)M, &b->tmp)) return rc;
+    if (int rc = dalloc(&b->d_keys, (size_t)M, nullptr)) return rc;
+    int cell_bits = 0;
+    while (((uint64_t)1 << cell_bits) < num_cells) ++cell_bits;
+    RTC_CU(cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, d_keys_in, b->d_keys, (int)M, 0, 32 + cell_bits, st));
+    uint8_t* d_temp = nullptr;
+    if (int rc = dalloc(&d_temp, std::max(scan_bytes, sort_bytes), &b->tmp)) return rc;
+    RTC_CU(cub::DeviceScan::ExclusiveSum(d_temp, scan_bytes, d_count, d_begin, (int)num_cells, st));
+    const uint32_t stats_init[3] = { 0u, 0xFFFFFFFFu, 0u };
+    RTC_CU(cudaMemcpyAsync(d_stats, stats_init, sizeof stats_init, cudaMemcpyHostToDevice, st));
+    k_cells<<<(unsigned)((num_cells + kThreads - 1) / kThreads), kThreads, 0, st>>>(d_count, d_begin, (uint32_t)num_cells, b->d_cells, d_stats);
+
+    // initIndices: emit the (cell, triangle) keys, sort
+    if (M) {
+        RTC_CU(cudaMemsetAsync(d_cursor, 0, 2 * sizeof(unsigned long long), st));
+        o.keys = d_keys_in;
+        k_bin<true><<<tri_blocks, kThreads, 0, st>>>(b->d_pos, num_tris, g, o);
+        k_bin_big<true><<<148 * 8, kThreads, 0, st>>>(b->d_pos, g, o);
+        RTC_CU(cub::DeviceRadixSort::SortKeys(d_temp, sort_bytes, d_keys_in, b->d_keys, (int)M, 0, 32 + cell_bits, st));
+    }
+    RTC_CU(cudaEventRecord(e1, st));
+    uint32_t h_stats[3];
+    RTC_CU(cudaMemcpyAsync(h_stats, d_stats, sizeof h_stats, cudaMemcpyDeviceToHost, st));
+    RTC_CU(cudaMemcpyAsync(h_cursor, d_cursor, sizeof h_cursor, cudaMemcpyDeviceToHost, st));
+    RTC_CU(cudaStreamSynchronize(st));
+    RTC_CU(cudaGetLastError());
+    if (M && h_cursor[0] != M) return rtc_fail_(RTC_ERR_CUDA, "grid build: the emit pass produced %llu keys, the count pass %llu", h_cursor[0], (unsigned long long)M);
+    // stage2.zig:76-100 initialises min to maxInt and max to 0; the host build reports the same values
+    b->empty_cells = h_stats[0]; b->min_tris = h_stats[1]; b->max_tris = h_stats[2];
+    RTC_CU(cudaEventElapsedTime(&b->device_ms, e0, e1));
+    for (void* p : b->tmp) cudaFree(p);
+    b->tmp.clear();
+    return RTC_OK;
+}
+
+}  // namespace build
+}  // namespace rtc
+
+using rtc::build::kThreads;
+
+static int check_soup_args(const float* positions, const rtc_tri_data* data, uint32_t num_tris, const uint32_t* res)
+{
+    if ((num_tris && (!positions || !data)) || !res || !res[0] || !res[1] || !res[2])
+        return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "null triangle soup or zero grid resolution");
+    return RTC_OK;
+}
+
+static int pick_device(int* device)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return rtc_fail_(RTC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU fallback)"); }
+    if (*device < 0) RTC_CU(cudaGetDevice(device));
+    if (*device >= n) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "device %d of %d", *device, n);
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, *device) != cudaSuccess || p.major != 10)
+        return rtc_fail_(RTC_ERR_NO_DEVICE, "device %d is not sm_100 (kernels are built for sm_100a only)", *device);
+    return RTC_OK;
+}
+
+extern "C" int rtc_geometry_build_device(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
+                                         const uint32_t res[3], int device, rtc_geometry* out)
+{
+    if (!out) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "rtc_geometry_build_device: out is null");
+    memset(out, 0, sizeof *out);
+    if (int rc = check_soup_args(positions, data, num_tris, res)) return rc;
+    if (int rc = pick_device(&device)) return rc;
+    RtcDeviceGuard guard(device);
+    try {
+        rtc::build::Built b;
+        if (int rc = rtc::build::grid_build(positions, data, num_tris, res, nullptr, &b)) return rc;
+        std::unique_ptr<RtcGeometryOwner> own(new RtcGeometryOwner());
+        own->cells.resize(b.num_cells);
+        own->tri_pos.resize(b.num_baked);
+        own->tri_data.resize(b.num_baked);
+        static_assert(sizeof(rtc_cell) == sizeof(uint2) && sizeof(rtc_tri_pos) == 3 * sizeof(float4), "ABI layouts");
+        RTC_CU(cudaMemcpy(own->cells.data(), b.d_cells, b.num_cells * sizeof(uint2), cudaMemcpyDeviceToHost));
+        if (b.num_baked) {
+            float4* d_tp = nullptr; uint32_t* d_td = nullptr;
+            if (int rc = rtc::build::dalloc(&d_tp, 3 * (size_t)b.num_baked, &b.tmp)) return rc;
+            if (int rc = rtc::build::dalloc(&d_td, 17 * (size_t)b.num_baked, &b.tmp)) return rc;
+            rtc::build::k_bake_aos<<<(unsigned)((b.num_baked + kThreads - 1) / kThreads), kThreads>>>(b.d_keys, b.num_baked, b.d_pos, b.d_data, d_tp, d_td);
+            RTC_CU(cudaGetLastError());
+            RTC_CU(cudaMemcpy(own->tri_pos.data(), d_tp, b.num_baked * sizeof(rtc_tri_pos), cudaMemcpyDeviceToHost));
+            RTC_CU(cudaMemcpy(own->tri_data.data(), d_td, b.num_baked * sizeof(rtc_tri_data), cudaMemcpyDeviceToHost));
+        }
+        out->grid = b.grid;
+        out->cells = own->cells.data(); out->num_cells = b.num_cells;
+        out->tri_pos = own->tri_pos.data(); out->tri_data = own->tri_data.data();
+        out->num_tris = b.num_baked; out->num_src_tris = num_tris;
+        out->empty_cells = b.empty_cells; out->min_tris = b.min_tris; out->max_tris = b.max_tris;
+        out->owner = own.release();
+        return RTC_OK;
+    } catch (const std::bad_alloc&) {
+        return rtc_fail_(RTC_ERR_OUT_OF_MEMORY, "rtc_geometry_build_device: host allocation failed");
+    }
+}
+
+extern "C" int rtc_scene_create_from_soup(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
+                                          const uint32_t res[3], const rtc_material* materials, uint32_t num_materials,
+                                          int device, rtc_scene** out, rtc_build_info* info)
+{
+    if (!out) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_create_from_soup: out is null");
+    *out = nullptr;
+    if (info) memset(info, 0, sizeof *info);
+    if (int rc = check_soup_args(positions, data, num_tris, res)) return rc;
+    for (int a = 0; a < 3; ++a)
+        if (res[a] > rtc::kMaxGridRes)
+            return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)", res[a], a, rtc::kMaxGridRes);
+    rtc_scene* s = nullptr;
+    if (int rc = rtc_scene_new_(device, &s)) return rc;
+    RtcDeviceGuard guard(s->device);
+    const auto t0 = std::chrono::steady_clock::now();
+    auto body = [&]() -> int {
+        rtc::build::Built b;
+        if (int rc = rtc::build::grid_build(positions, data, num_tris, res, nullptr, &b)) return rc;
+        rtc::DevScene& d = s->dev;
+        for (int i = 0; i < 3; ++i) {
+            d.bmin[i] = b.grid.bbox_min[i]; d.bmax[i] = b.grid.bbox_max[i];
+            d.res[i] = b.grid.resolution[i]; d.cell[i] = b.grid.cell_size[i];
+        }
+        const size_t nb = rtc_scene_set_packing_(d, res);
+        uint2* d_cells = nullptr; unsigned long long* d_fine = nullptr; uint32_t* d_coarse = nullptr;
+        float4* d_pos = nullptr; uint32_t* d_data = nullptr; uint32_t* d_flag = nullptr;
+        const size_t M = (size_t)b.num_baked;
+        if (int rc = s->alloc(&d_cells, nb * 64)) return rc;
+        if (int rc = s->alloc(&d_fine, nb)) return rc;
+        if (int rc = s->alloc(&d_coarse, (size_t)d.coarse_words)) return rc;
+        if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
+        if (int rc = s->alloc(&d_data, 20 * (size_t)num_tris)) return rc;
+        if (int rc = rtc::build::dalloc(&d_flag, 1, &b.tmp)) return rc;
+        RTC_CU(cudaMemset(d_cells, 0, nb * 64 * sizeof(uint2)));
+        RTC_CU(cudaMemset(d_fine, 0, nb * sizeof(unsigned long long)));
+        RTC_CU(cudaMemset(d_coarse, 0, (size_t)d.coarse_words * sizeof(uint32_t)));
+        RTC_CU(cudaMemset(d_flag, 0, sizeof(uint32_t)));
+        rtc::build::GridP g;
+        rtc::build::Packing pk;
+        for (int a = 0; a < 3; ++a) { g.bmin[a] = b.grid.bbox_min[a]; g.cell[a] = b.grid.cell_size[a]; g.res[a] = res[a]; pk.shift[a] = d.shift[a]; }
+        rtc::build::k_layout<<<(unsigned)((b.num_cells + kThreads - 1) / kThreads), kThreads>>>(b.d_cells, g, pk, d_cells, d_fine, d_coarse);
+        if (M) rtc::build::k_bake_soa<<<(unsigned)((M + kThreads - 1) / kThreads), kThreads>>>(b.d_keys, M, b.d_pos, d_pos, d_pos + M, d_pos + 2 * M);
+        if (num_tris) {
+            const uint64_t words = (uint64_t)num_tris * 20u;
+            rtc::build::k_pack_data<<<(unsigned)((words + kThreads - 1) / kThreads), kThreads>>>(b.d_data, num_tris, num_materials, d_data, d_flag);
+        }
+        RTC_CU(cudaGetLastError());
+        uint32_t flag = 0;
+        RTC_CU(cudaMemcpy(&flag, d_flag, sizeof flag, cudaMemcpyDeviceToHost));
+        if (flag) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "a triangle references a material index >= %u", num_materials);
+        d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse;
+        d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = (const float4*)d_data;
+        s->num_tris = b.num_baked; s->num_src_tris = num_tris;
+        if (info) {
+            info->grid = b.grid; info->num_cells = b.num_cells; info->num_tris = b.num_baked; info->num_src_tris = num_tris;
+            info->empty_cells = b.empty_cells; info->min_tris = b.min_tris; info->max_tris = b.max_tris;
+            info->device_ms = b.device_ms;
+        }
+        if (int rc = rtc_scene_upload_materials_(s, materials, num_materials)) return rc;
+        return rtc_scene_finish_(s);
+    };
+    const int rc = body();
+    if (rc != RTC_OK) { rtc_keep_error_free_(s); return rc; }
+    if (info) info->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    *out = s;
+    return RTC_OK;
+}

@@ -129,22 +129,35 @@ int main(int argc, char** argv)
 
     // stage2: Geometry.build + bakeInto, then the upload that stands where the Zig scene arena is filled
     t = Clock::now();
-    rtc_geometry geo;
-    if (rtc_geometry_build(host.positions, host.tri_data, host.num_tris, config.grid_resolution, &geo) != RTC_OK) return die("grid build");
-    fprintf(stderr, "info: Grid resolution: { %u, %u, %u }\n", geo.grid.resolution[0], geo.grid.resolution[1], geo.grid.resolution[2]);
-    fprintf(stderr, "info: Empty cells: %u/%llu (%.2f%%) min triangles: %u max triangles: %u mean_triangles: %llu\n", geo.empty_cells,
-            (unsigned long long)geo.num_cells, geo.num_cells ? 100.0 * geo.empty_cells / (double)geo.num_cells : 0.0, geo.min_tris, geo.max_tris,
-            (unsigned long long)(geo.num_cells > geo.empty_cells ? geo.num_tris / (geo.num_cells - geo.empty_cells) : 0));
-    fprintf(stderr, "info: Unique triangle count: %u/%llu (%.2f%%)\n", geo.num_src_tris, (unsigned long long)geo.num_tris,
-            geo.num_tris ? 100.0 * geo.num_src_tris / (double)geo.num_tris : 0.0);
-    rtc_scene_desc desc;
-    memset(&desc, 0, sizeof desc);
-    desc.grid = geo.grid; desc.cells = geo.cells; desc.num_cells = geo.num_cells;
-    desc.tri_pos = geo.tri_pos; desc.tri_data = geo.tri_data; desc.num_tris = geo.num_tris;
-    desc.materials = host.materials; desc.num_materials = host.num_materials; desc.num_src_tris = geo.num_src_tris;
+    // The grid is built and baked on the device (rtc_scene_create_from_soup); RTC_HOST_BUILD=1 keeps the
+    // host-thread build + upload of the baked arrays (same scene bit for bit).
+    fprintf(stderr, "info: Grid resolution: { %u, %u, %u }\n", config.grid_resolution[0], config.grid_resolution[1], config.grid_resolution[2]);
     rtc_scene* scene = nullptr;
-    if (rtc_scene_create(&desc, args.device, &scene) != RTC_OK) return die("scene upload");
-    rtc_geometry_free(&geo);
+    rtc_build_info bi;
+    memset(&bi, 0, sizeof bi);
+    const char* host_build = getenv("RTC_HOST_BUILD");
+    if (host_build && host_build[0] == '1') {
+        rtc_geometry geo;
+        if (rtc_geometry_build(host.positions, host.tri_data, host.num_tris, config.grid_resolution, &geo) != RTC_OK) return die("grid build");
+        bi.grid = geo.grid; bi.num_cells = geo.num_cells; bi.num_tris = geo.num_tris; bi.num_src_tris = geo.num_src_tris;
+        bi.empty_cells = geo.empty_cells; bi.min_tris = geo.min_tris; bi.max_tris = geo.max_tris;
+        rtc_scene_desc desc;
+        memset(&desc, 0, sizeof desc);
+        desc.grid = geo.grid; desc.cells = geo.cells; desc.num_cells = geo.num_cells;
+        desc.tri_pos = geo.tri_pos; desc.tri_data = geo.tri_data; desc.num_tris = geo.num_tris;
+        desc.materials = host.materials; desc.num_materials = host.num_materials; desc.num_src_tris = geo.num_src_tris;
+        if (rtc_scene_create(&desc, args.device, &scene) != RTC_OK) return die("scene upload");
+        rtc_geometry_free(&geo);
+    } else {
+        if (rtc_scene_create_from_soup(host.positions, host.tri_data, host.num_tris, config.grid_resolution, host.materials,
+                                       host.num_materials, args.device, &scene, &bi) != RTC_OK)
+            return die("grid build");
+    }
+    fprintf(stderr, "info: Empty cells: %u/%llu (%.2f%%) min triangles: %u max triangles: %u mean_triangles: %llu\n", bi.empty_cells,
+            (unsigned long long)bi.num_cells, bi.num_cells ? 100.0 * bi.empty_cells / (double)bi.num_cells : 0.0, bi.min_tris, bi.max_tris,
+            (unsigned long long)(bi.num_cells > bi.empty_cells ? bi.num_tris / (bi.num_cells - bi.empty_cells) : 0));
+    fprintf(stderr, "info: Unique triangle count: %u/%llu (%.2f%%)\n", bi.num_src_tris, (unsigned long long)bi.num_tris,
+            bi.num_tris ? 100.0 * bi.num_src_tris / (double)bi.num_tris : 0.0);
     fprintf(stderr, "info: Compiled in %s\n", since(t).c_str());
 
     std::vector<uint8_t> img((size_t)host.camera.w * host.camera.h * 3);

@@ -7,6 +7,7 @@
 // Compiled with -ffp-contract=off: the overlap test decides which cells hold a triangle and must
 // evaluate exactly like the reference's fp32 code (src/linalg.zig:500-563).
 #include "../../include/rtc.h"
+#include "rtc_geometry_owner.h"
 
 #include <algorithm>
 #include <atomic>
@@ -123,12 +124,6 @@ void parallel_for(uint64_t n, uint64_t grain, F&& body)
     for (auto& t : th) t.join();
 }
 
-struct Owner {
-    std::vector<rtc_cell> cells;
-    std::vector<rtc_tri_pos> tri_pos;
-    std::vector<rtc_tri_data> tri_data;
-};
-
 }  // namespace
 
 extern "C" int rtc_geometry_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
@@ -158,7 +153,7 @@ extern "C" int rtc_geometry_build(const float* positions, const rtc_tri_data* da
             for (uint64_t t = t0; t < t1; ++t)
                 b.for_cells((uint32_t)t, [&](uint64_t cell) { count[cell].fetch_add(1, std::memory_order_relaxed); });
         });
-        std::unique_ptr<Owner> own(new Owner());
+        std::unique_ptr<RtcGeometryOwner> own(new RtcGeometryOwner());
         own->cells.resize(num_cells);
         uint64_t total = 0;
         uint32_t min_t = 0xFFFFFFFFu, max_t = 0, empty = 0;
@@ -216,6 +211,6 @@ extern "C" int rtc_geometry_build(const float* positions, const rtc_tri_data* da
 extern "C" void rtc_geometry_free(rtc_geometry* g)
 {
     if (!g) return;
-    delete static_cast<Owner*>(g->owner);
+    delete static_cast<RtcGeometryOwner*>(g->owner);
     memset(g, 0, sizeof *g);
 }

@@ -50,6 +50,11 @@ def lib():
     L.rtc_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
     L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
+    L.rtc_geometry_build_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int,
+                                            C.POINTER(abi.Geometry)]
+    L.rtc_scene_create_from_soup.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                             C.POINTER(abi.Material), C.c_uint32, C.c_int,
+                                             C.POINTER(C.c_void_p), C.POINTER(abi.BuildInfo)]
     L.rtc_geometry_free.argtypes = [C.POINTER(abi.Geometry)]
     L.rtc_geometry_free.restype = None
     L.rtc_config_load.argtypes = [C.c_char_p, C.POINTER(abi.Config)]
@@ -139,15 +144,22 @@ class Geometry:
     ignored on input); resolution: config.json's grid_resolution.
     """
 
-    def __init__(self, positions, tri_data, resolution):
+    def __init__(self, positions, tri_data, resolution, device=None):
+        """device=None: the host-thread build (rtc_geometry_build); an int: the same build on that GPU
+        (rtc_geometry_build_device, -1 = current device), bit-identical outputs."""
         positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 9)
         tri_data = np.ascontiguousarray(tri_data, dtype=TRI_DATA_DTYPE)
         if tri_data.shape[0] != positions.shape[0]:
             raise ValueError("positions and tri_data disagree on the triangle count")
         res = np.ascontiguousarray(resolution, dtype=np.uint32)
         g = abi.Geometry()
-        _check(lib().rtc_geometry_build(positions.ctypes.data, tri_data.ctypes.data, positions.shape[0],
-                                        res.ctypes.data, C.byref(g)))
+        if device is None:
+            _check(lib().rtc_geometry_build(C.c_void_p(positions.ctypes.data), C.c_void_p(tri_data.ctypes.data),
+                                            C.c_uint32(positions.shape[0]), C.c_void_p(res.ctypes.data), C.byref(g)))
+        else:
+            _check(lib().rtc_geometry_build_device(C.c_void_p(positions.ctypes.data), C.c_void_p(tri_data.ctypes.data),
+                                                   C.c_uint32(positions.shape[0]), C.c_void_p(res.ctypes.data),
+                                                   C.c_int(device), C.byref(g)))
         try:
             nc, nt = int(g.num_cells), int(g.num_tris)
             self.grid = abi.Grid.from_buffer_copy(g.grid)
@@ -243,6 +255,26 @@ class Scene:
         self.desc, self._keep = make_scene_desc(geometry, materials)
         self._h = C.c_void_p()
         _check(lib().rtc_scene_create(C.byref(self.desc), device, C.byref(self._h)))
+
+    @classmethod
+    def from_soup(cls, positions, tri_data, resolution, materials, device=-1):
+        """geometry.build() + bakeInto + upload in one step with the grid built ON the device
+        (rtc_scene_create_from_soup). `build_info` holds what stage2 logs (src/stage2.zig:97-100,126-128)."""
+        positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 9)
+        tri_data = np.ascontiguousarray(tri_data, dtype=TRI_DATA_DTYPE)
+        if tri_data.shape[0] != positions.shape[0]:
+            raise ValueError("positions and tri_data disagree on the triangle count")
+        res = np.ascontiguousarray(resolution, dtype=np.uint32)
+        mats = (abi.Material * len(materials))(*[m.as_struct() for m in materials])
+        self = cls.__new__(cls)
+        self.desc, self._keep = None, (mats, materials)
+        self._h = C.c_void_p()
+        self.build_info = abi.BuildInfo()
+        _check(lib().rtc_scene_create_from_soup(C.c_void_p(positions.ctypes.data), C.c_void_p(tri_data.ctypes.data),
+                                                C.c_uint32(positions.shape[0]), C.c_void_p(res.ctypes.data),
+                                                mats, C.c_uint32(len(materials)), C.c_int(device),
+                                                C.byref(self._h), C.byref(self.build_info)))
+        return self
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
