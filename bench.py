@@ -154,13 +154,17 @@ def run_reference(args, rank, world):
     }))
 
 
-def workload_config(name, spec, geo, cam, spp, bounce, world):
+def workload_config(name, spec, geo, cam, spp, bounce, world, tiles=0):
     if OVERRIDE.get("spp") or OVERRIDE.get("height"):
         name = "%s [override spp=%s height=%s]" % (name, OVERRIDE.get("spp") or "-", OVERRIDE.get("height") or "-")
+    sharding = "none"
+    if world > 1:
+        sharding = ("strips of %d rows dealt round-robin, scene replicated, one NCCL gather of the RGB8 strips" % tiles) if tiles \
+            else "sample ranges, scene replicated, NCCL reduce(sum) of float4 accumulators"
     return {"workload": name, "scene": spec.name, "source_triangles": spec.num_tris, "baked_triangles": geo.num_tris,
             "grid": [int(x) for x in geo.grid.resolution], "width": int(cam.w), "height": int(cam.h),
-            "spp_per_gpu": spp, "spp_total": spp * world, "max_bounce": bounce, "seed": SEED,
-            "sharding": "sample ranges, scene replicated, NCCL reduce(sum) of float4 accumulators" if world > 1 else "none",
+            "spp_per_gpu": spp, "spp_total": spp if tiles else spp * world, "max_bounce": bounce, "seed": SEED,
+            "sharding": sharding,
             "l2": "flushed between timed steps by writing a 512 MiB buffer", "math": "exact (no FMA contraction)"}
 
 
@@ -189,9 +193,15 @@ def run_gpu(args, rank, world, local_rank):
         sb.close()
     P = cam.w * cam.h
     math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
-    total = spp * world                             # weak scaling: the frame's sample count grows with N
-    s_off, s_cnt = shard.sample_shard(rank, world, total)
-    prm = rtc.make_params(num_samples=s_cnt, max_bounce=bounce, seed=SEED, sample_offset=s_off, total_samples=total, math=math)
+    tiles = args.tile_rows if (args.sharding == "tiles" and world > 1) else 0
+    if tiles:
+        total = spp                                 # strong scaling: the frame is fixed, its pixels are dealt over the ranks
+        prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, total_samples=total, math=math,
+                              tile_rank=rank, tile_world=world, tile_rows=tiles)
+    else:
+        total = spp * world                         # weak scaling: the frame's sample count grows with N
+        s_off, s_cnt = shard.sample_shard(rank, world, total)
+        prm = rtc.make_params(num_samples=s_cnt, max_bounce=bounce, seed=SEED, sample_offset=s_off, total_samples=total, math=math)
     acc = torch.zeros(P, 4, device=dev)
     d_rgb = torch.zeros(P * 3, dtype=torch.uint8, device=dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
@@ -207,6 +217,12 @@ def run_gpu(args, rank, world, local_rank):
         if ev_k0: ev_k0.record()
         scene.render_accumulate(cam, prm, acc.data_ptr(), stream)
         if ev_k1: ev_k1.record()
+        if tiles:
+            rtc.resolve(acc.data_ptr(), P, total, d_rgb.data_ptr(), None, device=local_rank, stream_ptr=stream)
+            frame = shard.gather_strips(d_rgb.view(cam.h, cam.w, 3), tiles, dst=0)      # the path's only collective
+            if rank == 0 and frame.data_ptr() != d_rgb.data_ptr():
+                d_rgb.copy_(frame.reshape(-1))
+            return
         shard.reduce_accumulators(acc, dst=0)       # the path's only collective (no-op at N = 1)
         if rank == 0:
             rtc.resolve(acc.data_ptr(), P, total, d_rgb.data_ptr(), None, device=local_rank, stream_ptr=stream)
@@ -236,7 +252,7 @@ def run_gpu(args, rank, world, local_rank):
     trace_ms = st["trace_ms"] / args.steps                     # rank 0's k_trace launches, CUDA events per launch
     trace_launches = st["trace_launches"] / args.steps
     rays_per_step = float(r[0]) / args.steps
-    launches = int(r[2]) + (args.steps if rank == 0 or world == 1 else 0)      # + rank 0's resolve per step
+    launches = int(r[2]) + args.steps * (world if tiles else 1)               # + the resolve(s) per step
     value = rays_per_step / (step_ms * 1e-3) / 1e6
 
     # ---- e2e: the blocking public call, host buffers, D2H of the frame inside the timed region ----
@@ -270,7 +286,8 @@ def run_gpu(args, rank, world, local_rank):
     if rank == 0:
         # instrumented launch of the same frame: counts behind the algorithmic bytes
         prm_s = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, sample_offset=0, total_samples=total,
-                                math=math, collect_stats=True)
+                                math=math, collect_stats=True, tile_rank=rank if tiles else 0, tile_world=world if tiles else 0,
+                                tile_rows=tiles)
         acc.zero_(); torch.cuda.synchronize()
         scene.stats()
         scene.render_accumulate(cam, prm_s, acc.data_ptr(), stream)
@@ -284,7 +301,7 @@ def run_gpu(args, rank, world, local_rank):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = trav_bytes / (max(trace_ms, 1e-9) * 1e-3) / 1e9
-        cfg = workload_config(args.workload, spec, geo, cam, spp, bounce, world)
+        cfg = workload_config(args.workload, spec, geo, cam, spp, bounce, world, tiles)
         cfg["math"] = "exact (no FMA contraction)" if math == abi.RTC_MATH_EXACT else "fast (FMA contraction)"
         cfg["host_build_s"] = round(build_s, 3); cfg["scene_upload_s"] = round(upload_s, 3)
         cfg["device_build"] = device_build
@@ -292,7 +309,7 @@ def run_gpu(args, rank, world, local_rank):
                           "bytes": round(algo_bytes / cs["rays"], 1), "rays_per_path": round(cs["rays"] / cs["paths"], 3)}
         out = {
             "metric": "Mrays/s", "value": round(value, 2), "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "strong" if tiles else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
             "e2e": {"value": round(e2e_val, 2), "unit": "Mrays/s", "ms_per_frame": round(e2e_s * 1e3, 3),
                     "h2d_bytes_per_step": 56 + 48, "d2h_bytes_per_step": P * 3,
@@ -337,6 +354,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--sharding", default="samples", choices=["samples", "tiles"],
+                    help="N > 1: sample ranges + reduce (weak scaling, default) or row strips + gather (strong scaling, cfg4)")
+    ap.add_argument("--tile-rows", type=int, default=8, help="--sharding tiles: rows per strip")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--cpu-rows", type=int, default=0, help="--impl reference: rows per step (0 = calibrate to ~8 s)")

@@ -148,10 +148,11 @@ typedef struct rtc_params {
     uint32_t total_samples;  /* frame total used for the 1/S scale; 0 = num_samples */
     uint32_t accel;          /* RTC_ACCEL_* */
     uint32_t math;           /* RTC_MATH_* */
-    uint32_t tile_rank;      /* tile sharding: this call renders 8x4-pixel tiles t with  */
-    uint32_t tile_world;     /* (t / tile_group) % tile_world == tile_rank; 0/1 = all    */
-    uint32_t collect_stats;  /* nonzero: run the instrumented kernels, fill rtc_aux.stats */
-    uint32_t reserved;
+    uint32_t tile_rank;      /* pixel sharding: this call renders the pixels of rank tile_rank of   */
+    uint32_t tile_world;     /* tile_world (0/1 = all pixels); see tile_rows                        */
+    uint32_t collect_stats;  /* nonzero: run the instrumented kernels, fill rtc_aux.stats           */
+    uint32_t tile_rows;      /* 0: one contiguous band of rows per rank, rows [h*r/n, h*(r+1)/n);   */
+                             /* k>0: strips of k full rows dealt round-robin, strip i -> rank i % n */
 } rtc_params;
 
 /* Counters behind SURVEY §8(d)'s bytes-per-ray figure. */

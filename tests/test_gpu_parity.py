@@ -6,7 +6,7 @@ asserted), radiance within 1e-3 relative RMSE."""
 import numpy as np
 import pytest
 
-from zig_raytracing_contest_b200 import abi, rtc, scenes
+from zig_raytracing_contest_b200 import abi, rtc, scenes, shard
 
 pytestmark = pytest.mark.gpu
 
@@ -109,6 +109,20 @@ def test_sample_sharding_and_row_sharding(orc, setups):
     h2 = cam.h // 2
     assert np.array_equal(_bits(rad[0][:h2]), _bits(full["radiance"][:h2]))
     assert np.array_equal(_bits(rad[1][h2:]), _bits(full["radiance"][h2:]))
+    # strips of k rows dealt round-robin over 3 "ranks" (the last strip is short when k does not divide h)
+    for rows in (1, 5, 16, 1000):
+        img2 = np.zeros((cam.h, cam.w, 3), np.uint8)
+        rad2 = np.zeros((cam.h, cam.w, 3), np.float32)
+        paths = 0
+        for r in range(3):
+            out = scene.render(cam, rtc.make_params(num_samples=8, seed=3, tile_rank=r, tile_world=3, tile_rows=rows), img=img2,
+                               want_radiance=True, want_stats=True)
+            paths += out["stats"]["paths"]
+            for a, b in shard.strips_of(r, 3, cam.h, rows):
+                rad2[a:b] = out["radiance"][a:b]
+        assert paths == cam.w * cam.h * 8                          # every pixel rendered by exactly one rank
+        assert np.array_equal(img2, full["rgb"])
+        assert np.array_equal(_bits(rad2), _bits(full["radiance"]))
     import torch
     acc = torch.zeros(cam.h * cam.w, 4, device="cuda:0")
     for r in range(2):

@@ -36,6 +36,16 @@ def test_row_band_tiles_the_frame():
             assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
 
 
+def test_strips_tile_the_frame():
+    for h in (1, 7, 27, 1080, 2160):
+        for world in (1, 2, 3, 8):
+            for rows in (1, 4, 8, 4000):
+                got = sorted(sum((shard.strips_of(r, world, h, rows) for r in range(world)), []))
+                assert got[0][0] == 0 and got[-1][1] == h
+                assert all(got[i][1] == got[i + 1][0] for i in range(len(got) - 1))
+                assert all(b - a == rows for a, b in got[:-1])
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -67,10 +77,16 @@ def _worker(rank, world, port, out_dir):
     full_prm = rtc.make_params(num_samples=S, max_bounce=3, seed=11)
     band = oracle.render(desc, cam, full_prm, num_threads=1, rows=(y0, y1))["rgb"][y0:y1]
     frame = shard.gather_row_bands(torch.from_numpy(band.copy()), cam.w, cam.h, dst=0)
+    # ---- row strips dealt round-robin + gather (cam.h = 27 rows, strips of 4: the last strip is short) ----
+    mine = torch.zeros(cam.h, cam.w, 3, dtype=torch.uint8)
+    for a, b in shard.strips_of(rank, world, cam.h, 4):
+        mine[a:b] = torch.from_numpy(oracle.render(desc, cam, full_prm, num_threads=1, rows=(a, b))["rgb"][a:b].copy())
+    frame2 = shard.gather_strips(mine, 4, dst=0)
     if rank == 0:
         ref = oracle.render(desc, cam, full_prm, num_threads=1)
         np.save(os.path.join(out_dir, "acc.npy"), acc.numpy())
         np.save(os.path.join(out_dir, "frame.npy"), frame.numpy())
+        np.save(os.path.join(out_dir, "frame2.npy"), frame2.numpy())
         np.save(os.path.join(out_dir, "ref_rad.npy"), ref["radiance"])
         np.save(os.path.join(out_dir, "ref_rgb.npy"), ref["rgb"])
     dist.barrier()
@@ -85,3 +101,4 @@ def test_two_ranks_reproduce_the_single_frame(tmp_path, orc):
     assert (acc[:, 3] == 6).all()                                    # every sample rendered exactly once
     np.testing.assert_allclose(acc[:, :3] / 6.0, ref_rad, rtol=3e-6, atol=1e-7)   # fp32 sum reordering only
     assert np.array_equal(np.load(tmp_path / "frame.npy"), np.load(tmp_path / "ref_rgb.npy"))
+    assert np.array_equal(np.load(tmp_path / "frame2.npy"), np.load(tmp_path / "ref_rgb.npy"))

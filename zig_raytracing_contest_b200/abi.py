@@ -80,7 +80,7 @@ class Params(C.Structure):        # rtc_params
                 ("sample_offset", C.c_uint32), ("total_samples", C.c_uint32),
                 ("accel", C.c_uint32), ("math", C.c_uint32),
                 ("tile_rank", C.c_uint32), ("tile_world", C.c_uint32),
-                ("collect_stats", C.c_uint32), ("reserved", C.c_uint32)]
+                ("collect_stats", C.c_uint32), ("tile_rows", C.c_uint32)]
 
 
 class Stats(C.Structure):         # rtc_stats

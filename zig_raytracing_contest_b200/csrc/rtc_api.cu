@@ -322,14 +322,40 @@ int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_param
     return RTC_OK;
 }
 
-// Rows [y0,y1) of the frame that this call renders. Tile sharding = contiguous bands of rows:
-// rank r of n owns rows [r*h/n, (r+1)*h/n) (the reference's own split is contiguous pixel ranges
-// per worker, src/stage3.zig:228-233).
-void shard_rows(const rtc_camera* cam, const rtc_params* p, uint32_t* y0, uint32_t* y1)
+// The pixels of the frame that this call renders (partitioning A). tile_world <= 1: all.
+// tile_rows == 0: one contiguous band of rows per rank, rank r of n owns rows [r*h/n, (r+1)*h/n) (the reference's
+// own split is contiguous pixel ranges per worker, src/stage3.zig:228-233). tile_rows > 0: strips of tile_rows
+// full rows dealt round-robin, strip k belongs to rank k % n — sky rows and geometry rows spread over every rank.
+struct Shard {
+    uint32_t first = 0, count = 0;          // first pixel; number of pixels this call renders
+    uint32_t strip_px = 0, stride_px = 0;   // stride_px == 0: contiguous
+    uint32_t full_strips = 0, tail_px = 0;  // interleaved: count = full_strips * strip_px + tail_px
+};
+Shard shard_pixels(const rtc_camera* cam, const rtc_params* p)
 {
-    if (p->tile_world <= 1) { *y0 = 0; *y1 = cam->h; return; }
-    *y0 = (uint32_t)(((uint64_t)cam->h * p->tile_rank) / p->tile_world);
-    *y1 = (uint32_t)(((uint64_t)cam->h * (p->tile_rank + 1)) / p->tile_world);
+    Shard sh;
+    const uint32_t P = cam->w * cam->h;
+    if (p->tile_world <= 1) { sh.count = P; return sh; }
+    if (p->tile_rows == 0) {
+        const uint32_t y0 = (uint32_t)(((uint64_t)cam->h * p->tile_rank) / p->tile_world);
+        const uint32_t y1 = (uint32_t)(((uint64_t)cam->h * (p->tile_rank + 1)) / p->tile_world);
+        sh.first = y0 * cam->w; sh.count = (y1 - y0) * cam->w;
+        return sh;
+    }
+    const uint32_t rows = p->tile_rows < cam->h ? p->tile_rows : cam->h;
+    const uint32_t nstrips = (cam->h + rows - 1) / rows;
+    sh.strip_px = rows * cam->w;
+    sh.stride_px = sh.strip_px * p->tile_world;
+    sh.first = sh.strip_px * p->tile_rank;
+    if (p->tile_rank < nstrips) {
+        const uint32_t mine = (nstrips - 1 - p->tile_rank) / p->tile_world + 1;     // strips rank, rank+n, ...
+        const uint32_t last = p->tile_rank + (mine - 1) * p->tile_world;
+        const uint32_t last_px = last == nstrips - 1 ? P - last * sh.strip_px : sh.strip_px;
+        sh.full_strips = last_px == sh.strip_px ? mine : mine - 1;
+        sh.tail_px = last_px == sh.strip_px ? 0 : last_px;
+        sh.count = sh.full_strips * sh.strip_px + sh.tail_px;
+    }
+    return sh;
 }
 
 // Wavefront scratch for `slots` path slots and `levels` scattering levels (rtc_device.cuh WaveScratch).
@@ -388,12 +414,11 @@ int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels
 int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, float4* accum,
                   rtc::PrimaryOut pout, cudaStream_t stream)
 {
-    uint32_t y0, y1;
-    shard_rows(cam, p, &y0, &y1);
+    const Shard sh = shard_pixels(cam, p);
     rtc::DevParams dp;
     dp.num_samples = p->num_samples; dp.max_bounce = p->max_bounce; dp.sample_offset = p->sample_offset;
     dp.seed_lo = (uint32_t)p->seed; dp.seed_hi = (uint32_t)(p->seed >> 32);
-    dp.first_pixel = y0 * cam->w; dp.num_pixels = (y1 - y0) * cam->w;
+    dp.first_pixel = sh.first; dp.num_pixels = sh.count; dp.strip_px = sh.strip_px; dp.stride_px = sh.stride_px;
     const bool primary = p->mode == RTC_MODE_PRIMARY;
     if (int rc = ensure_wave(s, dp.num_pixels, primary ? 1u : p->num_samples, primary ? 1u : p->max_bounce)) return rc;
     const rtc::DevCamera dc = to_dev(*cam);
@@ -463,9 +488,10 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t
     if (int rc = ensure_frame(s, pixels)) return rc;
     const uint32_t total = p->mode == RTC_MODE_PRIMARY ? 1u : (p->total_samples ? p->total_samples : p->num_samples);
     if (total == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "num_samples is zero");
-    uint32_t y0, y1;
-    shard_rows(cam, p, &y0, &y1);
-    const size_t first = (size_t)y0 * cam->w, count = (size_t)(y1 - y0) * cam->w;
+    const Shard sh = shard_pixels(cam, p);
+    // the span of the frame buffers this call touches: its band, or (interleaved strips) the whole frame
+    const bool strips = sh.stride_px != 0;
+    const size_t first = strips ? 0 : sh.first, count = strips ? pixels : sh.count;
     const bool want_hits = p->mode == RTC_MODE_PRIMARY && aux && (aux->hit_id || aux->hit_tuv);
     const bool want_rad = aux && aux->radiance;
     cudaStream_t st = s->stream;
@@ -480,20 +506,42 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
     s->launches += 1;
     CU(cudaEventRecord(s->ev1, st));
-    // D2H through the pinned staging buffer (rgb_out is pageable caller memory, src/main.zig:122).
+    // D2H of this call's pixels through the pinned staging buffer (rgb_out is pageable caller memory,
+    // src/main.zig:122), compacted: a band is one copy, interleaved strips are one strided 2-D copy (+ the short tail).
     uint8_t* h_rgb = s->h_pinned;
-    float* h_rad = (float*)(s->h_pinned + (size_t)pixels * 3);
-    uint32_t* h_id = (uint32_t*)(s->h_pinned + (size_t)pixels * 15);
-    float* h_tuv = (float*)(s->h_pinned + (size_t)pixels * 19);
-    CU(cudaMemcpyAsync(h_rgb, s->d_rgb + 3 * first, count * 3, cudaMemcpyDeviceToHost, st));
-    if (want_rad) CU(cudaMemcpyAsync(h_rad, s->d_radiance + 3 * first, count * 12, cudaMemcpyDeviceToHost, st));
-    if (want_hits && aux->hit_id) CU(cudaMemcpyAsync(h_id, s->d_hit_id + first, count * 4, cudaMemcpyDeviceToHost, st));
-    if (want_hits && aux->hit_tuv) CU(cudaMemcpyAsync(h_tuv, s->d_hit_tuv + 3 * first, count * 12, cudaMemcpyDeviceToHost, st));
+    uint8_t* h_rad = s->h_pinned + (size_t)pixels * 3;
+    uint8_t* h_id = s->h_pinned + (size_t)pixels * 15;
+    uint8_t* h_tuv = s->h_pinned + (size_t)pixels * 19;
+    auto fetch = [&](const void* d_base, size_t elem, uint8_t* stage) -> cudaError_t {
+        const uint8_t* src = (const uint8_t*)d_base + elem * sh.first;
+        if (!strips) return cudaMemcpyAsync(stage, src, elem * sh.count, cudaMemcpyDeviceToHost, st);
+        cudaError_t r = cudaSuccess;
+        if (sh.full_strips)
+            r = cudaMemcpy2DAsync(stage, elem * sh.strip_px, src, elem * sh.stride_px, elem * sh.strip_px, sh.full_strips, cudaMemcpyDeviceToHost, st);
+        if (r == cudaSuccess && sh.tail_px)
+            r = cudaMemcpyAsync(stage + elem * sh.strip_px * sh.full_strips, src + elem * (size_t)sh.stride_px * sh.full_strips,
+                                elem * sh.tail_px, cudaMemcpyDeviceToHost, st);
+        return r;
+    };
+    auto scatter = [&](void* host_base, size_t elem, const uint8_t* stage) {
+        uint8_t* dst = (uint8_t*)host_base + elem * sh.first;
+        if (!strips) { memcpy(dst, stage, elem * sh.count); return; }
+        for (uint32_t k = 0; k < sh.full_strips; ++k) memcpy(dst + elem * (size_t)sh.stride_px * k, stage + elem * (size_t)sh.strip_px * k, elem * sh.strip_px);
+        if (sh.tail_px) memcpy(dst + elem * (size_t)sh.stride_px * sh.full_strips, stage + elem * (size_t)sh.strip_px * sh.full_strips, elem * sh.tail_px);
+    };
+    if (sh.count) {
+        CU(fetch(s->d_rgb, 3, h_rgb));
+        if (want_rad) CU(fetch(s->d_radiance, 12, h_rad));
+        if (want_hits && aux->hit_id) CU(fetch(s->d_hit_id, 4, h_id));
+        if (want_hits && aux->hit_tuv) CU(fetch(s->d_hit_tuv, 12, h_tuv));
+    }
     CU(cudaStreamSynchronize(st));
-    memcpy(rgb_out + 3 * first, h_rgb, count * 3);
-    if (want_rad) memcpy(aux->radiance + 3 * first, h_rad, count * 12);
-    if (want_hits && aux->hit_id) memcpy(aux->hit_id + first, h_id, count * 4);
-    if (want_hits && aux->hit_tuv) memcpy(aux->hit_tuv + 3 * first, h_tuv, count * 12);
+    if (sh.count) {
+        scatter(rgb_out, 3, h_rgb);
+        if (want_rad) scatter(aux->radiance, 12, h_rad);
+        if (want_hits && aux->hit_id) scatter(aux->hit_id, 4, h_id);
+        if (want_hits && aux->hit_tuv) scatter(aux->hit_tuv, 12, h_tuv);
+    }
     if (aux && aux->stats) {
         if (int rc = read_counters(s, aux->stats)) return rc;
         float ms = 0.0f;

@@ -64,8 +64,13 @@ struct DevParams {
     uint32_t max_bounce;
     uint32_t sample_offset;
     uint32_t seed_lo, seed_hi;
-    uint32_t first_pixel;    // pixel range of this call: [first_pixel, first_pixel + num_pixels)
+    // pixels of this call, as a list of num_pixels LOCAL indices pl -> frame pixel (slot_pixel):
+    //   stride_px == 0 : the contiguous range [first_pixel, first_pixel + num_pixels)
+    //   stride_px != 0 : strips of strip_px pixels dealt round-robin over the ranks; this rank's k-th strip
+    //                    starts at first_pixel + k * stride_px (the frame's last strip may be short)
+    uint32_t first_pixel;
     uint32_t num_pixels;
+    uint32_t strip_px, stride_px;
 };
 static constexpr uint32_t kMaxBounce = 64;
 
@@ -88,11 +93,20 @@ struct WaveScratch {
 };
 // one batch: pixels [first_pixel, +num_pixels) x samples [s0, s0+ns) (absolute sample indices)
 struct WaveParams {
-    uint32_t first_pixel, num_pixels;
+    uint32_t first_pixel, num_pixels;     // num_pixels local pixels starting at local index pl0
     uint32_t s0, ns;
     uint32_t max_bounce;
     uint32_t seed_lo, seed_hi;
+    uint32_t pl0, strip_px, stride_px;    // DevParams' pixel list
 };
+// local pixel index of the batch -> frame pixel
+__device__ __forceinline__ uint32_t slot_pixel(const WaveParams& wp, uint32_t pl)
+{
+    pl += wp.pl0;
+    if (wp.stride_px == 0u) return wp.first_pixel + pl;
+    const uint32_t k = pl / wp.strip_px;
+    return wp.first_pixel + k * wp.stride_px + (pl - k * wp.strip_px);
+}
 // counters[]: 0 rays, 1 cells_visited, 2 tris_tested, 3 hits_shaded, 4 paths
 enum { CNT_RAYS = 0, CNT_CELLS = 1, CNT_TRIS = 2, CNT_HITS = 3, CNT_PATHS = 4, CNT_N = 8 };
 

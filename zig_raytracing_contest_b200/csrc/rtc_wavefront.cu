@@ -176,7 +176,7 @@ k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam
         QueuedRay e;
         if (on) {
             const uint32_t sl = slot / wp.num_pixels, pl = slot - sl * wp.num_pixels;
-            const uint32_t pixel = wp.first_pixel + pl;
+            const uint32_t pixel = slot_pixel(wp, pl);
             const float x = (float)(pixel % cam.w), y = (float)(pixel / cam.w);
             cn.paths += 1;
             float4 leaf = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));     // depth == 0 -> zeroes (stage3.zig:189-191)
@@ -397,7 +397,7 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
             uint32_t top = __float_as_uint(__ldg(&qin.a3[i].w));
             Ray ray; ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
             const uint32_t sl = slot / wp.num_pixels, pl = slot - sl * wp.num_pixels;
-            const uint32_t pixel = wp.first_pixel + pl;
+            const uint32_t pixel = slot_pixel(wp, pl);
             v3 leaf = splat(0.0f);
             if (h.y == kMiss) {
                 leaf = env_color(ray.d);
@@ -470,7 +470,8 @@ k_accum(const __grid_constant__ WaveParams wp, const __grid_constant__ WaveScrat
 {
     const uint32_t pl = blockIdx.x * kThreads + threadIdx.x;
     if (pl >= wp.num_pixels) return;
-    float4 a = accum[wp.first_pixel + pl];
+    const uint32_t pixel = slot_pixel(wp, pl);
+    float4 a = accum[pixel];
     for (uint32_t sl = 0; sl < wp.ns; ++sl) {
         const uint32_t slot = sl * wp.num_pixels + pl;
         const float4 lf = ws.leaf[slot];
@@ -484,7 +485,7 @@ k_accum(const __grid_constant__ WaveParams wp, const __grid_constant__ WaveScrat
         a.x = a.x + value.x; a.y = a.y + value.y; a.z = a.z + value.z;
     }
     a.w = a.w + (float)wp.ns;
-    accum[wp.first_pixel + pl] = a;
+    accum[pixel] = a;
 }
 
 // img[i] = pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:223,242):
@@ -549,7 +550,8 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
         const uint32_t s_chunk = ws.cap / np < S ? ws.cap / np : S;
         for (uint32_t s0 = 0; s0 < S; s0 += s_chunk) {
             WaveParams wp;
-            wp.first_pixel = prm.first_pixel + p0; wp.num_pixels = np;
+            wp.first_pixel = prm.first_pixel; wp.num_pixels = np;
+            wp.pl0 = p0; wp.strip_px = prm.strip_px; wp.stride_px = prm.stride_px;
             wp.s0 = prm.sample_offset + s0; wp.ns = S - s0 < s_chunk ? S - s0 : s_chunk;
             wp.max_bounce = B; wp.seed_lo = prm.seed_lo; wp.seed_hi = prm.seed_hi;
             cudaError_t e = cudaMemsetAsync(ws.counts, 0, 2 * (kMaxBounce + 1) * sizeof(uint32_t), cfg.stream);

@@ -237,13 +237,15 @@ def make_scene_desc(geometry, materials):
 
 
 def make_params(num_samples=3, max_bounce=4, mode=abi.RTC_MODE_PATH, seed=0, sample_offset=0,
-                total_samples=0, math=abi.RTC_MATH_EXACT, tile_rank=0, tile_world=0, collect_stats=False):
+                total_samples=0, math=abi.RTC_MATH_EXACT, tile_rank=0, tile_world=0, collect_stats=False,
+                tile_rows=0):
     """main.Config's num_samples / max_bounce (src/main.zig:56-61; config.json defaults 3 and 4)."""
     p = abi.Params()
     p.num_samples, p.max_bounce, p.mode, p.seed = num_samples, max_bounce, mode, seed
     p.sample_offset, p.total_samples = sample_offset, total_samples
     p.accel, p.math = abi.RTC_ACCEL_GRID, math
     p.tile_rank, p.tile_world, p.collect_stats = tile_rank, tile_world, 1 if collect_stats else 0
+    p.tile_rows = tile_rows
     return p
 
 

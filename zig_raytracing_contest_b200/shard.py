@@ -7,6 +7,8 @@ keyed by absolute (pixel, sample). Two partitions, both without a collective ins
   sample ranges : rank r renders samples [offset, offset+count) of every pixel into a float4
                   accumulator; ONE reduce(SUM) to rank 0, which resolves (1/S, toRGB)
   row bands     : rank r renders rows [y0, y1) and the finished bands are gathered on rank 0
+  row strips    : strips of `rows` full rows dealt round-robin (strip i -> rank i % n), so sky rows and
+                  geometry rows spread over every rank; the finished strips are gathered on rank 0
 
 Works with any torch.distributed backend (nccl on the GPUs, gloo in the CPU tests).
 """
@@ -26,7 +28,7 @@ def sample_shard(rank, world, total_samples):
 
 def row_band(rank, world, height):
     """Rows [y0, y1) of `rank` — the same split rtc_render applies for tile_rank/tile_world
-    (csrc/rtc_api.cu shard_rows): y0 = h*r/n, y1 = h*(r+1)/n."""
+    (csrc/rtc_api.cu shard_pixels, tile_rows = 0): y0 = h*r/n, y1 = h*(r+1)/n."""
     if world < 1 or not 0 <= rank < world:
         raise ValueError("rank %d of %d" % (rank, world))
     return (height * rank) // world, (height * (rank + 1)) // world
@@ -59,3 +61,41 @@ def gather_row_bands(band, width, height, dst=0, group=None):
         y0, y1 = row_band(r, world, height)
         frame[y0:y1] = out[r][:y1 - y0]
     return frame
+
+
+def strips_of(rank, world, height, rows):
+    """Row ranges [(y0, y1), ...] of `rank` when strips of `rows` rows are dealt round-robin — the split
+    rtc_render applies for tile_rows > 0 (csrc/rtc_api.cu shard_pixels)."""
+    if world < 1 or not 0 <= rank < world or rows < 1:
+        raise ValueError("rank %d of %d, %d rows per strip" % (rank, world, rows))
+    nstrips = (height + rows - 1) // rows
+    return [(k * rows, min(height, (k + 1) * rows)) for k in range(rank, nstrips, world)]
+
+
+def gather_strips(frame, rows, dst=0, group=None):
+    """Assemble the frame from per-rank strips with ONE gather. `frame` is [H, W, C] on every rank with
+    this rank's strips filled in; returns the complete frame on rank `dst`, None elsewhere."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if world == 1:
+        return frame
+    H = frame.shape[0]
+    nstrips = (H + rows - 1) // rows
+    per_rank = (nstrips + world - 1) // world
+    row_elems = int(frame[0].numel())
+    padded = frame
+    if nstrips * rows != H:                       # the last strip is short: pad so strips are equal-sized
+        padded = torch.zeros((nstrips * rows,) + tuple(frame.shape[1:]), dtype=frame.dtype, device=frame.device)
+        padded[:H] = frame
+    view = padded.reshape(nstrips, rows * row_elems)
+    mine = view[rank::world]
+    compact = torch.zeros((per_rank, rows * row_elems), dtype=frame.dtype, device=frame.device)
+    compact[:mine.shape[0]] = mine
+    out = [torch.empty_like(compact) for _ in range(world)] if rank == dst else None
+    dist.gather(compact, out, dst=dst, group=group)
+    if rank != dst:
+        return None
+    for r in range(world):
+        n_r = len(range(r, nstrips, world))
+        view[r::world] = out[r][:n_r]
+    return padded[:H]
