@@ -186,11 +186,13 @@ def run_gpu(args, rank, world, local_rank):
     if rank == 0:
         # the same scene built and baked ON the device from the triangle soup (not timed as part
         # of a step; reported beside the host-thread build it replaces)
-        sb = rtc.Scene.from_soup(spec.positions, spec.tri_data, geo.grid.resolution, spec.materials, device=local_rank)
-        bi = sb.build_info
+        for _ in range(2):                          # the first call pays the lazy loading of the build kernels
+            sb = rtc.Scene.from_soup(spec.positions, spec.tri_data, geo.grid.resolution, spec.materials, device=local_rank)
+            bi = sb.build_info
+            sb.close()
         assert (int(bi.num_tris), int(bi.empty_cells)) == (geo.num_tris, geo.empty_cells), "device build disagrees with the host build"
-        device_build = {"kernels_ms": round(float(bi.device_ms), 3), "call_ms": round(float(bi.total_ms), 1)}
-        sb.close()
+        device_build = {"kernels_ms": round(float(bi.device_ms), 3), "call_ms": round(float(bi.total_ms), 1),
+                        "note": "rtc_scene_create_from_soup, second call: grid-build kernels (CUDA events) / whole call incl. H2D of the soup and textures"}
     P = cam.w * cam.h
     math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
     tiles = args.tile_rows if (args.sharding == "tiles" and world > 1) else 0

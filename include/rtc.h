@@ -245,7 +245,7 @@ typedef struct rtc_build_info {
     uint32_t num_src_tris;
     uint32_t empty_cells;
     uint32_t min_tris, max_tris;
-    float    device_ms;      /* CUDA-event time of the build kernels (after the soup's H2D copy) */
+    float    device_ms;      /* CUDA-event time of the grid-build kernels (bbox, binning, scan, sort)         */
     double   total_ms;       /* wall time of the whole call: upload + build + bake + textures    */
 } rtc_build_info;
 

@@ -7,8 +7,9 @@ out=gpurun_out; mkdir -p $out
 run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N "$@"; }
 run > $out/${tag}_n${N}_cfg3.json 2> $out/${tag}_n${N}_cfg3.err; echo "cfg3 rc=$?"
 run --workload cfg4_terrain5M_4k_256spp --sharding tiles --steps 3 > $out/${tag}_n${N}_cfg4_tiles.json 2> $out/${tag}_n${N}_cfg4_tiles.err; echo "cfg4 rc=$?"
-for total in 16 64 256 1024 4096; do
+for total in ${SWEEP:-16 64 256 1024 4096}; do
   spp=$((total / N)); [ $spp -lt 1 ] && continue
-  run --workload cfg4_terrain5M_4k_256spp --spp $spp --steps 2 > $out/${tag}_n${N}_cfg5_spp${total}.json 2> $out/${tag}_n${N}_cfg5_spp${total}.err; echo "cfg5 $total rc=$?"
+  steps=2; [ $total -ge 1024 ] && steps=1
+  run --workload cfg4_terrain5M_4k_256spp --spp $spp --steps $steps > $out/${tag}_n${N}_cfg5_spp${total}.json 2> $out/${tag}_n${N}_cfg5_spp${total}.err; echo "cfg5 $total rc=$?"
 done
 echo done

@@ -333,17 +333,17 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     const uint64_t num_cells = (uint64_t)res[0] * res[1] * res[2];
     if (num_cells >= ((uint64_t)1 << 32)) return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid has 2^32 cells or more");
     b->num_cells = num_cells; b->num_src = num_tris;
-    cudaEvent_t e0, e1;
-    RTC_CU(cudaEventCreate(&e0));
-    RTC_CU(cudaEventCreate(&e1));
-    struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ e0, e1 };
+    // device time = three bracketed kernel groups (bbox | count | scan, cells, emit, sort); the cudaMallocs and the
+    // two small D2H reads between them (the grid box, the baked-triangle total) are host-side and not counted
+    cudaEvent_t ev[6];
+    for (cudaEvent_t& e : ev) RTC_CU(cudaEventCreate(&e));
+    struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 6; ++i) cudaEventDestroy(e[i]); } } evg{ ev };
 
     if (int rc = dalloc(&b->d_pos, (size_t)num_tris * 9, nullptr)) return rc;
     if (int rc = dalloc(&b->d_data, (size_t)num_tris * 17, nullptr)) return rc;
     if (int rc = dalloc(&b->d_cells, (size_t)num_cells, nullptr)) return rc;
     RTC_CU(cudaMemcpyAsync(b->d_pos, positions, (size_t)num_tris * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
     RTC_CU(cudaMemcpyAsync(b->d_data, data, (size_t)num_tris * sizeof(rtc_tri_data), cudaMemcpyHostToDevice, st));
-    RTC_CU(cudaEventRecord(e0, st));
 
     // initGrid
     int* d_box = nullptr;
@@ -351,10 +351,12 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     const int box_init[6] = { 0x7F800000, 0x7F800000, 0x7F800000, (int)0x807FFFFF, (int)0x807FFFFF, (int)0x807FFFFF };
     RTC_CU(cudaMemcpyAsync(d_box, box_init, sizeof box_init, cudaMemcpyHostToDevice, st));
     const uint64_t nv = (uint64_t)num_tris * 3;
+    RTC_CU(cudaEventRecord(ev[0], st));
     if (nv) {
         const unsigned gridx = (unsigned)std::min<uint64_t>((nv + kThreads - 1) / kThreads, 148u * 8u);
         k_bbox<<<gridx, kThreads, 0, st>>>(b->d_pos, nv, d_box);
     }
+    RTC_CU(cudaEventRecord(ev[1], st));
     int box[6];
     RTC_CU(cudaMemcpyAsync(box, d_box, sizeof box, cudaMemcpyDeviceToHost, st));
     RTC_CU(cudaStreamSynchronize(st));
@@ -377,10 +379,12 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     RTC_CU(cudaMemsetAsync(d_cursor, 0, 2 * sizeof(unsigned long long), st));
     BinOut o; o.count = d_count; o.keys = nullptr; o.cursor = d_cursor; o.big = d_big;
     const unsigned tri_blocks = (num_tris + kThreads - 1) / kThreads;
+    RTC_CU(cudaEventRecord(ev[2], st));
     if (num_tris) {
         k_bin<false><<<tri_blocks, kThreads, 0, st>>>(b->d_pos, num_tris, g, o);
         k_bin_big<false><<<148 * 8, kThreads, 0, st>>>(b->d_pos, g, o);
     }
+    RTC_CU(cudaEventRecord(ev[3], st));
     unsigned long long h_cursor[2] = { 0, 0 };
     RTC_CU(cudaMemcpyAsync(h_cursor, d_cursor, sizeof h_cursor, cudaMemcpyDeviceToHost, st));
     RTC_CU(cudaStreamSynchronize(st));
@@ -399,6 +403,7 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     RTC_CU(cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, d_keys_in, b->d_keys, (int)M, 0, 32 + cell_bits, st));
     uint8_t* d_temp = nullptr;
     if (int rc = dalloc(&d_temp, std::max(scan_bytes, sort_bytes), &b->tmp)) return rc;
+    RTC_CU(cudaEventRecord(ev[4], st));
     RTC_CU(cub::DeviceScan::ExclusiveSum(d_temp, scan_bytes, d_count, d_begin, (int)num_cells, st));
     const uint32_t stats_init[3] = { 0u, 0xFFFFFFFFu, 0u };
     RTC_CU(cudaMemcpyAsync(d_stats, stats_init, sizeof stats_init, cudaMemcpyHostToDevice, st));
@@ -412,7 +417,7 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
         k_bin_big<true><<<148 * 8, kThreads, 0, st>>>(b->d_pos, g, o);
         RTC_CU(cub::DeviceRadixSort::SortKeys(d_temp, sort_bytes, d_keys_in, b->d_keys, (int)M, 0, 32 + cell_bits, st));
     }
-    RTC_CU(cudaEventRecord(e1, st));
+    RTC_CU(cudaEventRecord(ev[5], st));
     uint32_t h_stats[3];
     RTC_CU(cudaMemcpyAsync(h_stats, d_stats, sizeof h_stats, cudaMemcpyDeviceToHost, st));
     RTC_CU(cudaMemcpyAsync(h_cursor, d_cursor, sizeof h_cursor, cudaMemcpyDeviceToHost, st));
@@ -421,7 +426,8 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     if (M && h_cursor[0] != M) return rtc_fail_(RTC_ERR_CUDA, "grid build: the emit pass produced %llu keys, the count pass %llu", h_cursor[0], (unsigned long long)M);
     // stage2.zig:76-100 initialises min to maxInt and max to 0; the host build reports the same values
     b->empty_cells = h_stats[0]; b->min_tris = h_stats[1]; b->max_tris = h_stats[2];
-    RTC_CU(cudaEventElapsedTime(&b->device_ms, e0, e1));
+    b->device_ms = 0.0f;
+    for (int i = 0; i < 3; ++i) { float ms = 0.0f; RTC_CU(cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1])); b->device_ms += ms; }
     for (void* p : b->tmp) cudaFree(p);
     b->tmp.clear();
     return RTC_OK;
