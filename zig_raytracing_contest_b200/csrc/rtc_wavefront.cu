@@ -219,36 +219,12 @@ k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam
 // (stage3.zig:174) yields when triangles are tested in index order; the ray ends at the first cell whose
 // exit crossing is >= best.t (stage3.zig:179-182). The block occupancy masks only skip the cells[] load of
 // empty cells.
-#ifndef RTC_TWO_STAGE
-#define RTC_TWO_STAGE 1
-#endif
 struct TraceShared {
     float4 ro[32];                      // per lane: ray origin (.w unused)
     float4 rd[32];                      // per lane: ray direction
     unsigned long long best[32];        // per lane: min over the cell's (t bits << 32 | baked triangle index)
     uint2 item[32];                     // compacted pending list: {owner lane, begin - exclusive prefix}
-#if RTC_TWO_STAGE
-    uint2 surv[64];                     // (owner lane, baked triangle) pairs that passed the cheap reject, as a stack
-#endif
 };
-
-// The cheap, CONSERVATIVE part of Triangle.rayIntersection (src/linalg.zig:696-722): the exact culling test
-// `det < 1e-8`, and a reject on u that never drops a pair the exact code would keep. With det >= 1e-8 the exact
-// code computes u = x * (1/det), x = dot(o - v0, p), and rejects u < 0 || u > 1:
-//   x <= -2^-60 (and det < 2^60)  =>  x * (1/det) <= -2^-120 is a negative normal number  =>  u < 0
-//   x > det * 1.0001              =>  x * RN(1/det) > 1.00009, which cannot round down to 1  =>  u > 1
-// Everything else (including every NaN/inf case: all comparisons below are false) goes on to the exact test.
-// About 4 of 5 pairs end here, without the IEEE division and the second cross product.
-__device__ __forceinline__ bool tri_ray_maybe(v3 v0, v3 e1, v3 e2, const Ray& r)
-{
-    const v3 p = cross(r.d, e2);
-    const float det = dot(e1, p);
-    if (det < 0.00000001f) return false;
-    const float x = dot(r.o - v0, p);
-    if (x <= -8.673617379884035e-19f && det < 1.152921504606847e18f) return false;
-    if (x > det * 1.0001f) return false;
-    return true;
-}
 
 template <bool STATS, bool CSM>
 __global__ void __launch_bounds__(kTraceThreads, RTC_TRACE_MINB)
@@ -331,46 +307,6 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                 ws.best[lane] = ~0ull;
             }
             __syncwarp();
-#if RTC_TWO_STAGE
-            // Two stages. Stage 1 runs the cheap conservative reject on every pair at full lanes and pushes
-            // the survivors; stage 2 runs the exact test on 32 survivors at a time (the lanes that would have
-            // idled through the second half of the test are gone). The winner is a min over (t, index), so
-            // the order in which pairs reach stage 2 does not matter.
-            uint32_t nsurv = 0;                                 // uniform
-            auto exact_pass = [&](uint32_t first, uint32_t n) {
-                if (lane < n) {
-                    const uint2 e = ws.surv[first + lane];
-                    const float4 a = __ldg(sc.tri_v0 + e.y), b = __ldg(sc.tri_e1 + e.y), c = __ldg(sc.tri_e2 + e.y);
-                    const float4 o4 = ws.ro[e.x], d4 = ws.rd[e.x];
-                    Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
-                    float t, u, v;
-                    if (tri_ray(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), r, t, u, v) && t > 0.0f)
-                        atomicMin(&ws.best[e.x], ((unsigned long long)__float_as_uint(t) << 32) | e.y);
-                }
-            };
-            for (uint32_t base = 0; base < total; base += 32u) {
-                const bool mine = cnt != 0u && excl >= base && excl < base + 32u;
-                const uint32_t starts = __reduce_or_sync(kFull, mine ? 1u << (excl - base) : 0u);
-                const uint32_t before = __popc(__ballot_sync(kFull, cnt != 0u && excl < base));
-                const uint32_t j = base + lane;
-                bool keep = false;
-                uint2 e = make_uint2(0u, 0u);
-                if (j < total) {
-                    const uint2 it = ws.item[before + __popc(starts & le_mask) - 1u];
-                    e = make_uint2(it.x, j + it.y);
-                    const float4 a = __ldg(sc.tri_v0 + e.y), b = __ldg(sc.tri_e1 + e.y), c = __ldg(sc.tri_e2 + e.y);
-                    const float4 o4 = ws.ro[it.x], d4 = ws.rd[it.x];
-                    Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
-                    keep = tri_ray_maybe(mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), mk(c.x, c.y, c.z), r);
-                }
-                const uint32_t km = __ballot_sync(kFull, keep);
-                if (keep) ws.surv[nsurv + __popc(km & lt_mask)] = e;
-                nsurv += __popc(km);
-                __syncwarp();
-                if (nsurv >= 32u) { nsurv -= 32u; exact_pass(nsurv, 32u); __syncwarp(); }
-            }
-            if (nsurv != 0u) exact_pass(0u, nsurv);
-#else
             for (uint32_t base = 0; base < total; base += 32u) {
                 const bool mine = cnt != 0u && excl >= base && excl < base + 32u;
                 const uint32_t starts = __reduce_or_sync(kFull, mine ? 1u << (excl - base) : 0u);
@@ -387,7 +323,6 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                         atomicMin(&ws.best[it.x], ((unsigned long long)__float_as_uint(t) << 32) | ti);
                 }
             }
-#endif
             __syncwarp();
             // ---- phase C: owners fold the cell's winner in and take the cell's exit crossing ----
             if (cnt != 0u) {
