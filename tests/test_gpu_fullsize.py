@@ -1,0 +1,93 @@
+"""BASELINE.json's configurations at their FULL sizes. The oracle cannot render a whole 1080p/64 spp frame in
+seconds, so the checks are (a) bit-exact radiance against the oracle on bands of rows of the full frame (the
+RNG is keyed by absolute pixel and sample, so a band of the oracle's frame equals the same rows of the whole
+frame), and (b) size-independent properties of the whole frame: every path counted once, re-rendering is
+idempotent, and a frame assembled from shards (row strips; sample ranges) equals the unsharded frame."""
+import numpy as np
+import pytest
+
+from zig_raytracing_contest_b200 import abi, rtc, scenes, shard
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def cfg3():
+    spec = scenes.atrium()
+    geo = rtc.Geometry(spec.positions, spec.tri_data, (128, 128, 128))
+    scene = rtc.Scene(geo, spec.materials, device=0)
+    yield spec, geo, scene, spec.camera(height=1080)
+    scene.close()
+
+
+def test_cfg1_cfg2_primary_full_frame_bands(orc, cfg3):
+    """configs[0]/[1]: primary visibility at 1920x1080 — hit ids and t,u,v bit-exact on 6 bands of 12 rows."""
+    spec, geo, scene, cam = cfg3
+    assert (cam.w, cam.h) == (1920, 1080)
+    prm = rtc.make_params(mode=abi.RTC_MODE_PRIMARY)
+    g = scene.render(cam, prm, want_hits=True, want_radiance=True)
+    for y0 in (0, 200, 431, 640, 900, 1068):
+        o = orc.render(scene.desc, cam, prm, rows=(y0, y0 + 12), want_hits=True, want_radiance=True)
+        assert np.array_equal(g["hit_id"][y0:y0 + 12], o["hit_id"][y0:y0 + 12])
+        assert np.array_equal(_bits(g["hit_tuv"][y0:y0 + 12]), _bits(o["hit_tuv"][y0:y0 + 12]))
+        assert np.array_equal(_bits(g["radiance"][y0:y0 + 12]), _bits(o["radiance"][y0:y0 + 12]))
+    assert (g["hit_id"] != abi.MISS_ID).mean() > 0.5
+
+
+def test_cfg3_full_frame(orc, cfg3):
+    """configs[2]: 1920x1080, 64 spp, 4 bounces = 132.7 M paths in 6 batches."""
+    spec, geo, scene, cam = cfg3
+    prm = rtc.make_params(num_samples=64, max_bounce=4, seed=1)
+    g = scene.render(cam, prm, want_radiance=True, want_stats=True)
+    assert g["stats"]["paths"] == 1920 * 1080 * 64
+    assert g["stats"]["rays"] >= g["stats"]["paths"] and g["stats"]["rays"] <= 4 * g["stats"]["paths"]
+    assert np.isfinite(g["radiance"]).all() and g["radiance"].min() >= 0.0
+    # the oracle on three bands of 4 rows (bit-exact radiance, all 64 samples, all bounces)
+    for y0 in (100, 540, 1000):
+        o = orc.render(scene.desc, cam, prm, rows=(y0, y0 + 4), want_radiance=True)
+        assert np.array_equal(_bits(g["radiance"][y0:y0 + 4]), _bits(o["radiance"][y0:y0 + 4]))
+        assert np.abs(g["rgb"][y0:y0 + 4].astype(int) - o["rgb"][y0:y0 + 4].astype(int)).max() <= 1
+    # idempotence: the same call again gives the same bits (no state leaks between frames or batches)
+    g2 = scene.render(cam, prm, want_radiance=True)
+    assert np.array_equal(_bits(g["radiance"]), _bits(g2["radiance"])) and np.array_equal(g["rgb"], g2["rgb"])
+    # strips dealt over 4 "ranks" tile the frame bit for bit
+    img = np.zeros((cam.h, cam.w, 3), np.uint8)
+    for r in range(4):
+        scene.render(cam, rtc.make_params(num_samples=64, max_bounce=4, seed=1, tile_rank=r, tile_world=4, tile_rows=8), img=img)
+    assert np.array_equal(img, g["rgb"])
+
+
+def test_cfg4_scene_4k_bands(orc):
+    """configs[3]'s shape at a triangle count the oracle's serial build handles in seconds: procedural terrain
+    (1 M triangles), 3840x2160, camera inside the grid; 4 spp; two bands of 2 rows bit-exact, whole-frame
+    path count, and sample-range sharding (2 x 2 spp into one accumulator) equal to the 4 spp frame."""
+    spec = scenes.terrain(1_000_000)
+    scene = rtc.Scene.from_soup(spec.positions, spec.tri_data, (128, 128, 128), spec.materials, device=0)
+    geo = orc.Geometry(spec.positions, spec.tri_data, (128, 128, 128))
+    assert int(scene.build_info.num_tris) == geo.tri_pos.shape[0]
+    desc, keep = rtc.make_scene_desc(geo, spec.materials)
+    cam = spec.camera(height=2160)
+    assert (cam.w, cam.h) == (3840, 2160)
+    prm = rtc.make_params(num_samples=4, max_bounce=4, seed=1)
+    g = scene.render(cam, prm, want_radiance=True, want_stats=True)
+    assert g["stats"]["paths"] == 3840 * 2160 * 4
+    for y0 in (700, 1500):
+        o = orc.render(desc, cam, prm, rows=(y0, y0 + 2), want_radiance=True)
+        assert np.array_equal(_bits(g["radiance"][y0:y0 + 2]), _bits(o["radiance"][y0:y0 + 2]))
+    import torch
+    P = cam.w * cam.h
+    acc = torch.zeros(P, 4, device="cuda:0")
+    for r in range(2):
+        off, cnt = shard.sample_shard(r, 2, 4)
+        scene.render_accumulate(cam, rtc.make_params(num_samples=cnt, max_bounce=4, seed=1, sample_offset=off, total_samples=4), acc.data_ptr())
+    torch.cuda.synchronize()
+    rad = torch.zeros(P, 3, device="cuda:0")
+    rtc.resolve(acc.data_ptr(), P, 4, None, rad.data_ptr(), device=0)
+    torch.cuda.synchronize()
+    # same samples added in the same order into one accumulator: bit-identical to the single call
+    assert np.array_equal(_bits(rad.cpu().numpy().reshape(cam.h, cam.w, 3)), _bits(g["radiance"]))
+    scene.close()
