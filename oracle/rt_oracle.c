@@ -427,7 +427,12 @@ void orc_rng_block(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t bloc
  * z = 1-2*u1; (cos,sin)(2*pi*u2) by quadrant reduction + minimax polynomials on [-pi/4,pi/4]. */
 void orc_unit_vector(float u1, float u2, float out[3])
 {
-    const float z = 1.0f - 2.0f * u1;
+    /* u1 = k / 2^24 is taken at the CENTRE of its bin, z = 1 - 2 (k + 1/2) / 2^24 = (1 - 2^-24) - 2 u1 (both
+     * operations exact in f32), so the poles z = +-1 are never produced. With z = +-1 exactly, normal + unit
+     * vector cancels to the zero vector on every axis-aligned wall facing the pole (probability 2^-24 per
+     * bounce: a handful of NaN pixels per 1080p/64 spp frame); the reference's normalize(N(0,1)^3)
+     * (src/linalg.zig:140-148) has no such atom. */
+    const float z = 0.99999994f - 2.0f * u1;
     const float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
     const float t4 = u2 * 4.0f;
     const float kf = floorf(t4 + 0.5f);

@@ -121,3 +121,19 @@ def test_philox4x32_10_known_answers(orc):
     assert [hex(x) for x in orc.philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344],
                                               [0xa4093822, 0x299f31d0])] == \
         ["0xd16cfe09", "0x94fdcceb", "0x5001e420", "0x24126ea1"]
+
+
+def test_unit_vector_has_no_pole_atom(orc):
+    """The sphere map takes u1 at its bin centre: z = +-1 (where normal + unit vector cancels exactly on an
+    axis-aligned wall and normalize() yields NaN) is never produced; vectors are unit length and isotropic."""
+    top = 1.0 - 2.0 ** -24
+    for u1, z in ((0.0, top), (top, -top), (0.5, -2.0 ** -24)):
+        v = orc.unit_vector(u1, 0.3)
+        assert v[2] == np.float32(z) and abs(v[2]) < 1.0
+        assert abs(float(np.linalg.norm(v.astype(np.float64))) - 1.0) < 1e-6
+        assert v[0] != 0.0 or v[1] != 0.0
+    rng = np.random.RandomState(3)
+    k = rng.randint(0, 1 << 24, size=(20000, 2))
+    vs = np.array([orc.unit_vector(a / 16777216.0, b / 16777216.0) for a, b in k], np.float64)
+    assert np.abs(np.linalg.norm(vs, axis=1) - 1.0).max() < 1e-6
+    assert np.abs(vs.mean(axis=0)).max() < 0.02 and np.abs((vs ** 2).mean(axis=0) - 1.0 / 3.0).max() < 0.01

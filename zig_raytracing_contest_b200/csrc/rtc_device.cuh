@@ -317,7 +317,7 @@ __device__ __forceinline__ void rng_block(uint32_t seed_lo, uint32_t seed_hi, ui
 // (orc_unit_vector). Same distribution as Vec3.randomUnitVector (src/linalg.zig:140-148).
 __device__ __forceinline__ v3 unit_vector(float u1, float u2)
 {
-    const float z = 1.0f - 2.0f * u1;
+    const float z = 0.99999994f - 2.0f * u1;       // bin centre of u1: the poles z = +-1 never occur (see orc_unit_vector)
     const float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
     const float t4 = u2 * 4.0f;
     const float kf = floorf(t4 + 0.5f);
