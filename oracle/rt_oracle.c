@@ -203,6 +203,20 @@ static float grid_iter_next(grid_iter* it)
     return t;
 }
 
+/* Grid.traceRay's Iterator as constructed (linalg.zig:443-469): 5 x 3 words per ray =
+ * cell, exit, step (1 / 0xFFFFFFFF), t_delta, t_next_crossing. Returns 0 when traceRay returns null. */
+int orc_grid_iter_init(const rtc_grid* g, const float orig[3], const float dir[3], uint32_t out_u[9], float out_f[6])
+{
+    ray_t r = { v3_from(orig), v3_from(dir) };
+    grid_iter it;
+    if (!grid_trace_ray(g, r, &it)) return 0;
+    for (int i = 0; i < 3; ++i) {
+        out_u[i] = it.cell[i]; out_u[3 + i] = it.exit_[i]; out_u[6 + i] = it.step[i];
+        out_f[i] = it.t_delta[i]; out_f[3 + i] = it.t_next_crossing[i];
+    }
+    return 1;
+}
+
 int orc_grid_walk(const rtc_grid* g, const float orig[3], const float dir[3],
                   int max_steps, uint32_t* cells_xyz, float* t_next)
 {

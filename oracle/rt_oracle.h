@@ -64,6 +64,8 @@ void  orc_grid_cell_idx(const rtc_grid* g, const float p[3], uint32_t out[3]);
  * Returns the number of (cell, t) pairs written, or -1 when traceRay returns null. */
 int   orc_grid_walk(const rtc_grid* g, const float orig[3], const float dir[3],
                     int max_steps, uint32_t* cells_xyz, float* t_next);
+/* The Iterator Grid.traceRay constructs: out_u = cell[3], exit[3], step[3]; out_f = t_delta[3], t_next[3]. */
+int   orc_grid_iter_init(const rtc_grid* g, const float orig[3], const float dir[3], uint32_t out_u[9], float out_f[6]);
 int   orc_triangle_ray_intersection(const float v0[3], const float e1[3], const float e2[3],
                                     const float orig[3], const float dir[3],
                                     float* t, float* u, float* v);

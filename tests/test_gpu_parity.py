@@ -41,6 +41,10 @@ def test_primary_hit_ids_bit_exact(orc, setups, name):
     assert np.abs(g["rgb"].astype(int) - o["rgb"].astype(int)).max() <= 1
     for k in ("rays", "cells_visited", "tris_tested", "hits_shaded", "paths"):
         assert g["stats"][k] == o["stats"][k], k
+    # the production kernels (no counters: empty blocks taken in one step, csrc/rtc_trav.cuh) give the same bits
+    p = scene.render(cam, prm, want_hits=True, want_radiance=True)
+    assert np.array_equal(p["hit_id"], o["hit_id"]) and np.array_equal(_bits(p["hit_tuv"]), _bits(o["hit_tuv"]))
+    assert np.array_equal(_bits(p["radiance"]), _bits(o["radiance"]))
 
 
 @pytest.mark.parametrize("name", ["cornell", "atrium"])
@@ -74,6 +78,10 @@ def test_path_radiance_bit_exact(orc, setups, name, spp, bounce):
     for k in ("rays", "cells_visited", "tris_tested", "hits_shaded", "paths"):
         assert g["stats"][k] == o["stats"][k], k
     assert g["stats"]["paths"] == cam.w * cam.h * spp
+    # production kernels (no counters, two-level walk): same bits
+    p = scene.render(cam, prm, want_radiance=True)
+    assert np.array_equal(_bits(p["radiance"]), _bits(o["radiance"]))
+    assert np.array_equal(p["rgb"], g["rgb"])
 
 
 def test_fast_math_within_tolerance(orc, setups):

@@ -18,6 +18,7 @@
 // The first version of this path was one persistent megakernel (one lane = one path); its profile
 // (profiles/r1b_*) showed 16 of 32 lanes active and 25 % occupancy at 128 registers.
 #include "rtc_kernels.h"
+#include "rtc_trav.cuh"
 
 #ifndef RTC_NS
 #error "compile with -DRTC_NS=exact or -DRTC_NS=fast"
@@ -35,59 +36,14 @@ static constexpr uint32_t kFull = 0xFFFFFFFFu;
 #define RTC_TRACE_MINB 4
 #endif
 #ifndef RTC_KMAXSTEP
-#define RTC_KMAXSTEP 8
+#define RTC_KMAXSTEP 4
 #endif
+#ifndef RTC_TWO_LEVEL
+#define RTC_TWO_LEVEL 1
+#endif
+
 static constexpr int kMaxStep = RTC_KMAXSTEP;        // DDA steps a lane may take per round before the pooled triangle pass
 static constexpr uint32_t kChunk = 64;               // queue entries a warp reserves per atomic
-
-// ---------------------------------------------------------------------------------------------------------
-// Grid.Iterator (src/linalg.zig:471-497) in a register-lean form. The cell travels as the packed word of
-// rtc_device.cuh (low 6 bits = cell inside its 4x4x4 block, the rest = block index) next to the packed exit
-// cell; t_delta carries the step direction in its sign bit. The t_next_crossing / t_delta arithmetic is the
-// reference's, add for add. fine_lo/hi = occupancy mask of the block the cell lies in.
-struct Trav {
-    float tx, ty, tz;                   // t_next_crossing
-    float dx, dy, dz;                   // |.| = t_delta; sign bit set = stepping towards 0 on that axis
-    uint32_t c, ec;                     // packed cell, packed exit cell
-    uint32_t fine_lo, fine_hi;
-};
-
-// Occupancy of the block of cell s.c: the coarse bit (shared memory when CSM) decides whether the 8-byte fine
-// mask is fetched at all.
-template <bool CSM>
-__device__ __forceinline__ void trav_load_block(const DevScene& sc, const uint32_t* __restrict__ coarse, Trav& s)
-{
-    const uint32_t bi = s.c >> 6;
-    const uint32_t w = CSM ? coarse[bi >> 5] : __ldg(sc.coarse + (bi >> 5));
-    uint2 f = make_uint2(0u, 0u);
-    if ((w >> (bi & 31u)) & 1u) f = __ldg(reinterpret_cast<const uint2*>(sc.fine) + bi);
-    s.fine_lo = f.x; s.fine_hi = f.y;
-}
-__device__ __forceinline__ bool trav_occupied(const Trav& s)
-{
-    const uint32_t w = (s.c & 32u) ? s.fine_hi : s.fine_lo;
-    return ((w >> (s.c & 31u)) & 1u) != 0u;
-}
-
-// Iterator.next: axis = {2,1,2,1,2,2,0,0}[(tx<ty)<<2 | (tx<tz)<<1 | (ty<tz)] (linalg.zig:479-484):
-// x iff tx<ty && tx<tz; y iff !(tx<ty) && ty<tz; otherwise z (ties prefer z, then y). Returns +inf without
-// moving when the cell is the exit cell on that axis (linalg.zig:486-488). The coordinate of the axis is a
-// scattered bit field m of the packed cell: with every other bit set, +1 carries across the gap
-// ((c | ~m) + 1), and (c | ~m) + m == (c & m) - 1 is the decrement.
-__device__ __forceinline__ float trav_next(const DevScene& sc, Trav& s)
-{
-    const bool xy = s.tx < s.ty, xz = s.tx < s.tz, yz = s.ty < s.tz;
-    const bool ax = xy && xz, ay = !xy && yz;
-    const float t = ax ? s.tx : (ay ? s.ty : s.tz);
-    const float d = ax ? s.dx : (ay ? s.dy : s.dz);
-    const uint32_t m = ax ? sc.mask[0] : (ay ? sc.mask[1] : sc.mask[2]);
-    if (((s.c ^ s.ec) & m) == 0u) return __int_as_float(0x7f800000);
-    const uint32_t stepped = (s.c | ~m) + (__float_as_int(d) < 0 ? m : 1u);
-    s.c = (stepped & m) | (s.c & ~m);
-    const float tn = t + fabsf(d);
-    s.tx = ax ? tn : s.tx; s.ty = ay ? tn : s.ty; s.tz = ax ? s.tz : (ay ? s.tz : tn);
-    return t;
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // Ray queue entry (64 B, SoA over four float4 arrays): the ray and its DDA set-up.
@@ -110,6 +66,10 @@ __device__ __forceinline__ bool queue_setup(const DevScene& sc, const Ray& r, Qu
     q.dz = __uint_as_float(__float_as_uint(it.dz) | (it.sz == 1u ? 0u : 0x80000000u));
     q.c = pack_cell(sc.shift, it.cx, it.cy, it.cz);
     q.ec = pack_cell(sc.shift, it.ex, it.ey, it.ez);
+    // empty blocks are taken in one step (rtc_trav.cuh) unless the grid's boundary can lie inside a block or a
+    // crossing value is -inf / NaN (a -0.0 direction component): those rays walk cell by cell
+    const bool two_level = ((sc.res[0] | sc.res[1] | sc.res[2]) & 3u) == 0u && it.tx > -f_inf() && it.ty > -f_inf() && it.tz > -f_inf();
+    if (!two_level) q.ec |= kTravCellOnly;
     return true;
 }
 __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const QueuedRay& e)
@@ -231,6 +191,9 @@ __global__ void __launch_bounds__(kTraceThreads, RTC_TRACE_MINB)
 k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* __restrict__ count_ptr,
         uint32_t* __restrict__ head_ptr, uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
+    // The instrumented build counts every cell the reference visits, so it walks cell by cell; the production
+    // build takes empty blocks in one step (same triangle-holding cells, same t values: tests/test_trav_twolevel.py).
+    constexpr bool TWO = !STATS && RTC_TWO_LEVEL;
     __shared__ TraceShared s_ws[kTraceWarps];
     const uint32_t* coarse = stage_coarse<CSM>(sc);
     TraceShared& ws = s_ws[threadIdx.x >> 5];
@@ -277,6 +240,7 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
         }
         // ---- phase A: every live lane walks to its next non-empty cell (at most kMaxStep cells) ----
         uint32_t begin = 0, cnt = 0;
+        float enter_t = 0.0f;
         bool done = false;
         if (alive) {
 #pragma unroll 1
@@ -287,10 +251,9 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                     begin = c.x; cnt = c.y - c.x;
                     break;
                 }
-                const uint32_t c0 = s.c;
-                const float tn = trav_next(sc, s);
-                if (best_t <= tn) { done = true; break; }
-                if ((s.c ^ c0) >> 6) trav_load_block<CSM>(sc, coarse, s);
+                const uint32_t w = trav_advance<CSM, TWO>(sc, coarse, s, best_t, enter_t);
+                if (w == kWalkDone) { done = true; break; }
+                if (TWO && w >= kWalkEnter) trav_enter(s, enter_t, w - kWalkEnter);
             }
         }
         if (STATS) cn.tris += cnt;
@@ -329,10 +292,8 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                 const unsigned long long k = ws.best[lane];
                 const float t = __uint_as_float((uint32_t)(k >> 32));
                 if (k != ~0ull && best_t > t) { best_t = t; best_tri = (uint32_t)k; }
-                const uint32_t c0 = s.c;
-                const float tn = trav_next(sc, s);
-                if (best_t <= tn) done = true;
-                else if ((s.c ^ c0) >> 6) trav_load_block<CSM>(sc, coarse, s);
+                float unused_t;
+                if (trav_advance<CSM, TWO>(sc, coarse, s, best_t, unused_t) == kWalkDone) done = true;
             }
             __syncwarp();
         }
