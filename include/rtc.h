@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 5u
+#define RTC_ABI_VERSION 6u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -246,6 +246,7 @@ typedef struct rtc_build_info {
     uint32_t empty_cells;
     uint32_t min_tris, max_tris;
     float    device_ms;      /* CUDA-event time of the grid-build kernels (bbox, binning, scan, sort)         */
+    float    assemble_ms;    /* CUDA-event time of the triangle assembly (rtc_scene_create_from_gltf), else 0  */
     double   total_ms;       /* wall time of the whole call: upload + build + bake + textures    */
 } rtc_build_info;
 
@@ -291,6 +292,23 @@ typedef struct rtc_host_scene {
 int  rtc_gltf_load(const char* path, const char* camera_name, uint32_t width, uint32_t height,
                    int num_threads, rtc_host_scene* out);
 void rtc_host_scene_free(rtc_host_scene* scene);
+
+/* The same stage1 with loadTriangles' per-triangle loop (src/stage1.zig:235-255: index fetch, node transform
+ * of positions and normals, normalize, texcoords) ON the device: the file's buffers and one table row per
+ * primitive are uploaded, one sm_100a kernel writes the soup. Needs a GPU; results are bit-identical to
+ * rtc_gltf_load's (an out-of-range vertex index is the same RTC_ERR_FORMAT).
+ *
+ * rtc_scene_create_from_gltf = loadGltfFile .. bakeInto (src/main.zig:104-118) in one call: the soup never
+ * exists on the host, the grid is built and baked on the device from it (as rtc_scene_create_from_soup), and
+ * the scene renders bit-identically to rtc_gltf_load + rtc_geometry_build + rtc_scene_create. camera receives
+ * loadCamera's result (may be NULL); info may be NULL.
+ * rtc_gltf_load_device returns the device-assembled soup to the host in rtc_gltf_load's layout (parity checks,
+ * hosts that want the soup); free with rtc_host_scene_free. */
+int  rtc_scene_create_from_gltf(const char* path, const char* camera_name, uint32_t width, uint32_t height,
+                                int num_threads, const uint32_t grid_resolution[3], int device,
+                                rtc_scene** out, rtc_camera* camera, rtc_build_info* info);
+int  rtc_gltf_load_device(const char* path, const char* camera_name, uint32_t width, uint32_t height,
+                          int num_threads, int device, rtc_host_scene* out);
 
 /* stbi_write_png(path, w, h, 3, rgb, 3*w) of src/main.zig:130-135 (8-bit RGB, row 0 = top).
  * Returns RTC_OK / RTC_ERR_IO (stb returns 1 / 0). */

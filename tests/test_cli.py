@@ -10,6 +10,7 @@ import subprocess
 import numpy as np
 import pytest
 
+from gltf_cases import handmade, oracle_soup
 from zig_raytracing_contest_b200 import abi, gltf_io, rtc, scenes
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -101,6 +102,38 @@ def test_loader_size_rules_and_errors(tmp_path):
         rtc.HostSceneData(str(tmp_path / "nomat.gltf"), height=4)
 
 
+def test_loader_index_types_strides_alignment_match_oracle(orc, tmp_path):
+    """u8 / u16 / u32 indices, interleaved byteStride, accessors at unaligned offsets, no TEXCOORD_0, rotated
+    nested nodes: the host loader against the oracle's loadTriangles + zgltf transforms, bit for bit."""
+    path, doc, want = handmade(tmp_path, np.random.default_rng(5))
+    hs = rtc.HostSceneData(path, height=32)
+    wp, wd = oracle_soup(orc, doc, want)
+    assert len(hs.positions) == 50 + 900 + 211
+    assert np.array_equal(hs.positions.view(np.uint32), wp.view(np.uint32))
+    assert np.array_equal(hs.tri_data.view(np.uint8), wd.view(np.uint8))
+    assert (hs.camera.w, hs.camera.h) == (48, 32)
+    bad, _, _ = handmade(tmp_path, np.random.default_rng(6), bad_index=True)
+    with pytest.raises(rtc.RtcError) as e:
+        rtc.HostSceneData(bad, height=32)
+    assert e.value.code == abi.RTC_ERR_FORMAT
+
+
+def test_device_assembly_needs_a_device(tmp_path):
+    """rtc_gltf_load_device / rtc_scene_create_from_gltf have no host fallback."""
+    if rtc.device_count() > 0:
+        pytest.skip("a GPU is present")
+    path, _, _ = handmade(tmp_path, np.random.default_rng(5))
+    with pytest.raises(rtc.RtcError) as e:
+        rtc.HostSceneData(path, height=32, device=0)
+    assert e.value.code == abi.RTC_ERR_NO_DEVICE
+    with pytest.raises(rtc.RtcError) as e:
+        rtc.Scene.from_gltf(path, (8, 8, 8), height=32)
+    assert e.value.code == abi.RTC_ERR_NO_DEVICE
+    with pytest.raises(rtc.RtcError) as e:                 # file errors come first, as in the reference's order of work
+        rtc.Scene.from_gltf(str(tmp_path / "nope.gltf"), (8, 8, 8), height=32)
+    assert e.value.code == abi.RTC_ERR_IO
+
+
 def test_config_contract(tmp_path):
     p = str(tmp_path / "config.json")
     json.dump(CONFIG, open(p, "w"))
@@ -128,8 +161,9 @@ def test_png_roundtrip_and_decoder_colour_types(tmp_path):
     assert np.array_equal(rtc.png_read(str(tmp_path / "q.png")), rgba[:, :, :3])
 
 
-def _run_cli(cwd, *args):
-    return subprocess.run([CLI] + list(args), cwd=str(cwd), capture_output=True, text=True, timeout=300)
+def _run_cli(cwd, *args, env=None):
+    return subprocess.run([CLI] + list(args), cwd=str(cwd), capture_output=True, text=True, timeout=300,
+                          env=dict(os.environ, **env) if env else None)
 
 
 def test_cli_command_line_contract(tmp_path):
@@ -152,7 +186,10 @@ def test_cli_stops_at_the_device_boundary_without_gpu(tmp_path):
     json.dump(CONFIG, open(str(tmp_path / "config.json"), "w"))
     r = _run_cli(tmp_path, "--height=36")
     assert r.returncode != 0
-    assert "Loaded in" in r.stderr and "Preprocessed in" in r.stderr and "Grid resolution: { 16, 16, 16 }" in r.stderr
+    assert "Grid resolution: { 16, 16, 16 }" in r.stderr and "no CPU fallback" in r.stderr and "Rendered in" not in r.stderr
+    r = _run_cli(tmp_path, "--height=36", env={"RTC_HOST_LOAD": "1"})          # stage1 on the host: runs, then stops the same way
+    assert r.returncode != 0
+    assert "Loaded in" in r.stderr and "Preprocessed in" in r.stderr and "Materials count: 7" in r.stderr
     assert "no CPU fallback" in r.stderr and "Rendered in" not in r.stderr
     assert not os.path.exists(str(tmp_path / "output.png"))
 
@@ -164,9 +201,15 @@ def test_cli_renders_the_same_frame_as_the_binding(tmp_path):
     json.dump(CONFIG, open(str(tmp_path / "config.json"), "w"))
     r = _run_cli(tmp_path, "--in", "room.glb", "--out=frame.png", "--camera", "Camera 1", "--height", "72", "--seed", "5")
     assert r.returncode == 0, r.stderr
-    for phase in ("Loaded in", "Preprocessed in", "Compiled in", "Rendered in", "Saved in", "Done in"):
+    for phase in ("Loaded, preprocessed and compiled in", "triangle assembly", "Rendered in", "Saved in", "Done in"):
         assert phase in r.stderr
     got = rtc.png_read(str(tmp_path / "frame.png"))
+    for env in ({"RTC_HOST_LOAD": "1"}, {"RTC_HOST_BUILD": "1"}):      # stage1 / stage1+2 on the host: same frame
+        r = _run_cli(tmp_path, "--in", "room.glb", "--out=host.png", "--camera", "Camera 1", "--height", "72", "--seed", "5", env=env)
+        assert r.returncode == 0, r.stderr
+        for phase in ("Loaded in", "Preprocessed in", "Compiled in", "Rendered in", "Saved in", "Done in"):
+            assert phase in r.stderr
+        assert np.array_equal(rtc.png_read(str(tmp_path / "host.png")), got)
     hs = rtc.HostSceneData(str(tmp_path / "room.glb"), height=72)
     geo = rtc.Geometry(hs.positions, hs.tri_data, CONFIG["grid_resolution"])
     scene = rtc.Scene(geo, hs.materials, device=0)

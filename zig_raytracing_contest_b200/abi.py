@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 5
+RTC_ABI_VERSION = 6
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -111,7 +111,7 @@ class BuildInfo(C.Structure):     # rtc_build_info
     _fields_ = [("grid", Grid), ("num_cells", C.c_uint64), ("num_tris", C.c_uint64),
                 ("num_src_tris", C.c_uint32), ("empty_cells", C.c_uint32),
                 ("min_tris", C.c_uint32), ("max_tris", C.c_uint32),
-                ("device_ms", C.c_float), ("total_ms", C.c_double)]
+                ("device_ms", C.c_float), ("assemble_ms", C.c_float), ("total_ms", C.c_double)]
 
 
 class Config(C.Structure):        # rtc_config
@@ -132,6 +132,7 @@ EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
     "rtc_resolve", "rtc_scene_stats", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_geometry_build_device", "rtc_scene_create_from_soup",
+    "rtc_scene_create_from_gltf", "rtc_gltf_load_device",
     "rtc_last_error", "rtc_abi_version", "rtc_device_count",
     "rtc_config_load", "rtc_gltf_load", "rtc_host_scene_free", "rtc_png_write", "rtc_png_read",
 ]

@@ -19,11 +19,13 @@
 // Compiled with -fmad=false, IEEE div/sqrt: the overlap test decides which cells hold a triangle and must
 // evaluate exactly like the reference's fp32 code. CUB (scan, radix sort) is library plumbing of the build
 // step, not part of the render path.
+#include "rtc_gltf_plan.h"
 #include "rtc_internal.h"
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstring>
@@ -297,6 +299,82 @@ __global__ void __launch_bounds__(kThreads) k_bake_aos(const unsigned long long*
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// loadTriangles (src/stage1.zig:217-259) on the device: one thread per triangle of the soup. The primitive the
+// triangle belongs to is found by bisection over the table's first_tri column; the three indices are read in
+// their component type, range-checked against the accessors (flag[0] = a vertex index is out of range, what the
+// host loader reports as an error), the positions go through the node's global transform and the normals through
+// its direction part + normalize — the reference's fp32 operations in the reference's order (linalg.zig:263-278,
+// :119-125), this file being compiled without FMA contraction. Accessor data may sit at any byte offset (glTF
+// asks for 4-byte alignment, files in the wild do not always comply): unaligned words are put together from bytes.
+__device__ __forceinline__ uint32_t ld_u32_any(const uint8_t* p)
+{
+    if ((reinterpret_cast<uintptr_t>(p) & 3u) == 0u) return __ldg(reinterpret_cast<const uint32_t*>(p));
+    return (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8) | ((uint32_t)__ldg(p + 2) << 16) | ((uint32_t)__ldg(p + 3) << 24);
+}
+__device__ __forceinline__ v3 ld_v3_any(const uint8_t* p)
+{
+    return mk(__uint_as_float(ld_u32_any(p)), __uint_as_float(ld_u32_any(p + 4)), __uint_as_float(ld_u32_any(p + 8)));
+}
+__device__ __forceinline__ uint32_t ld_index(const uint8_t* p, uint32_t component)
+{
+    if (component == 5125u) return ld_u32_any(p);
+    if (component == 5123u) {
+        if ((reinterpret_cast<uintptr_t>(p) & 1u) == 0u) return __ldg(reinterpret_cast<const uint16_t*>(p));
+        return (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8);
+    }
+    return __ldg(p);
+}
+
+__global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict__ blob, const RtcPrimRef* __restrict__ prims, uint32_t num_prims,
+                                                       uint32_t num_tris, float* __restrict__ pos_out, uint32_t* __restrict__ data_out,
+                                                       uint32_t* __restrict__ flag)
+{
+    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;
+    if (g >= num_tris) return;
+    uint32_t lo = 0u, hi = num_prims;                       // last primitive with first_tri <= g
+    while (hi - lo > 1u) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(&prims[mid].first_tri) <= g) lo = mid; else hi = mid;
+    }
+    const RtcPrimRef& pr = prims[lo];
+    const uint32_t t = g - __ldg(&pr.first_tri);
+    const v3 c0 = mk(__ldg(&pr.m[0]), __ldg(&pr.m[1]), __ldg(&pr.m[2]));
+    const v3 c1 = mk(__ldg(&pr.m[4]), __ldg(&pr.m[5]), __ldg(&pr.m[6]));
+    const v3 c2 = mk(__ldg(&pr.m[8]), __ldg(&pr.m[9]), __ldg(&pr.m[10]));
+    const v3 c3 = mk(__ldg(&pr.m[12]), __ldg(&pr.m[13]), __ldg(&pr.m[14]));
+    const uint32_t comp = __ldg(&pr.index_component), has_uv = __ldg(&pr.has_uv);
+    const uint32_t s_ind = __ldg(&pr.stride_ind), s_pos = __ldg(&pr.stride_pos), s_nrm = __ldg(&pr.stride_nrm), s_uv = __ldg(&pr.stride_uv);
+    const uint8_t* b_ind = blob + __ldg(&pr.off_ind);
+    const uint8_t* b_pos = blob + __ldg(&pr.off_pos);
+    const uint8_t* b_nrm = blob + __ldg(&pr.off_nrm);
+    const uint8_t* b_uv = blob + __ldg(&pr.off_uv);
+    const uint32_t n_pos = __ldg(&pr.count_pos), n_nrm = __ldg(&pr.count_nrm), n_uv = __ldg(&pr.count_uv);
+    float* po = pos_out + 9 * (size_t)g;
+    uint32_t* dout = data_out + 17 * (size_t)g;
+    bool bad = false;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const uint32_t v = ld_index(b_ind + (size_t)(3u * t + (uint32_t)i) * s_ind, comp);
+        v3 p = mk(0.0f, 0.0f, 0.0f), n = p;
+        uint32_t uv0 = 0u, uv1 = 0u;
+        if (v >= n_pos || v >= n_nrm || (has_uv && v >= n_uv)) bad = true;
+        else {
+            const v3 vp = ld_v3_any(b_pos + (size_t)v * s_pos);
+            const v3 vn = ld_v3_any(b_nrm + (size_t)v * s_nrm);
+            p = ((scale(c0, vp.x) + scale(c1, vp.y)) + scale(c2, vp.z)) + c3;
+            n = normalize((scale(c0, vn.x) + scale(c1, vn.y)) + scale(c2, vn.z));   // not the inverse transpose (TODO in the reference)
+            if (has_uv) { uv0 = ld_u32_any(b_uv + (size_t)v * s_uv); uv1 = ld_u32_any(b_uv + (size_t)v * s_uv + 4); }
+        }
+        po[3 * i] = p.x; po[3 * i + 1] = p.y; po[3 * i + 2] = p.z;
+        dout[3 * i] = __float_as_uint(n.x); dout[3 * i + 1] = __float_as_uint(n.y); dout[3 * i + 2] = __float_as_uint(n.z);
+        dout[9 + 2 * i] = uv0; dout[10 + 2 * i] = uv1;
+    }
+    dout[15] = __ldg(&pr.material);
+    dout[16] = g;
+    if (bad) atomicOr(flag, 1u);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Host side of the build. Everything is allocated with cudaMalloc and owned by `Built` until released.
 struct Built {
     rtc_grid grid{};
@@ -308,6 +386,7 @@ struct Built {
     uint64_t num_cells = 0, num_baked = 0;
     uint32_t empty_cells = 0, min_tris = 0, max_tris = 0;
     float device_ms = 0.0f;
+    float assemble_ms = 0.0f;           // k_assemble (glTF plan -> soup), 0 when the soup came from the host
     std::vector<void*> tmp;             // scratch freed at the end of the build
     ~Built()
     {
@@ -327,9 +406,56 @@ static int dalloc(T** out, size_t count, std::vector<void*>* track)
     return RTC_OK;
 }
 
-static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t num_tris, const uint32_t res[3], cudaStream_t st, Built* b)
+// The soup from host memory: b->d_pos / b->d_data.
+static int soup_upload(const float* positions, const rtc_tri_data* data, uint32_t num_tris, cudaStream_t st, Built* b)
 {
     static_assert(sizeof(rtc_tri_data) == 17 * sizeof(uint32_t), "rtc_tri_data is 17 words");
+    if (int rc = dalloc(&b->d_pos, (size_t)num_tris * 9, nullptr)) return rc;
+    if (int rc = dalloc(&b->d_data, (size_t)num_tris * 17, nullptr)) return rc;
+    RTC_CU(cudaMemcpyAsync(b->d_pos, positions, (size_t)num_tris * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
+    RTC_CU(cudaMemcpyAsync(b->d_data, data, (size_t)num_tris * sizeof(rtc_tri_data), cudaMemcpyHostToDevice, st));
+    return RTC_OK;
+}
+
+// The soup from a glTF plan: the referenced buffers and the primitive table go up, k_assemble writes
+// b->d_pos / b->d_data.
+static int soup_assemble(const RtcGltfPlan& plan, cudaStream_t st, Built* b)
+{
+    static_assert(sizeof(rtc_tri_data) == 17 * sizeof(uint32_t), "rtc_tri_data is 17 words");
+    const uint32_t num_tris = plan.num_tris;
+    if (int rc = dalloc(&b->d_pos, (size_t)num_tris * 9, nullptr)) return rc;
+    if (int rc = dalloc(&b->d_data, (size_t)num_tris * 17, nullptr)) return rc;
+    if (!num_tris) return RTC_OK;
+    uint8_t* d_blob = nullptr; RtcPrimRef* d_prims = nullptr; uint32_t* d_flag = nullptr;
+    if (int rc = dalloc(&d_blob, (size_t)plan.blob_bytes + 16, &b->tmp)) return rc;
+    if (int rc = dalloc(&d_prims, plan.prims.size(), &b->tmp)) return rc;
+    if (int rc = dalloc(&d_flag, 1, &b->tmp)) return rc;
+    for (size_t i = 0; i < plan.buffers.size(); ++i)
+        if (plan.buffer_base[i] != ~(uint64_t)0 && !plan.buffers[i].empty())
+            RTC_CU(cudaMemcpyAsync(d_blob + plan.buffer_base[i], plan.buffers[i].data(), plan.buffers[i].size(), cudaMemcpyHostToDevice, st));
+    RTC_CU(cudaMemcpyAsync(d_prims, plan.prims.data(), plan.prims.size() * sizeof(RtcPrimRef), cudaMemcpyHostToDevice, st));
+    RTC_CU(cudaMemsetAsync(d_flag, 0, sizeof(uint32_t), st));
+    cudaEvent_t e0, e1;
+    RTC_CU(cudaEventCreate(&e0));
+    RTC_CU(cudaEventCreate(&e1));
+    struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ e0, e1 };
+    RTC_CU(cudaEventRecord(e0, st));
+    k_assemble<<<(num_tris + kThreads - 1) / kThreads, kThreads, 0, st>>>(d_blob, d_prims, (uint32_t)plan.prims.size(), num_tris, b->d_pos, b->d_data, d_flag);
+    RTC_CU(cudaEventRecord(e1, st));
+    uint32_t flag = 0;
+    RTC_CU(cudaMemcpyAsync(&flag, d_flag, sizeof flag, cudaMemcpyDeviceToHost, st));
+    RTC_CU(cudaStreamSynchronize(st));
+    RTC_CU(cudaGetLastError());
+    RTC_CU(cudaEventElapsedTime(&b->assemble_ms, e0, e1));
+    if (flag) return rtc_fail_(RTC_ERR_FORMAT, "glTF: vertex index out of range");
+    cudaFree(d_blob);                                   // the largest scratch: gone before the grid build allocates
+    b->tmp.erase(std::find(b->tmp.begin(), b->tmp.end(), (void*)d_blob));
+    return RTC_OK;
+}
+
+// The grid over the device-resident soup b->d_pos (num_tris triangles).
+static int grid_build(uint32_t num_tris, const uint32_t res[3], cudaStream_t st, Built* b)
+{
     const uint64_t num_cells = (uint64_t)res[0] * res[1] * res[2];
     if (num_cells >= ((uint64_t)1 << 32)) return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid has 2^32 cells or more");
     b->num_cells = num_cells; b->num_src = num_tris;
@@ -339,11 +465,7 @@ static int grid_build(const float* positions, const rtc_tri_data* data, uint32_t
     for (cudaEvent_t& e : ev) RTC_CU(cudaEventCreate(&e));
     struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 6; ++i) cudaEventDestroy(e[i]); } } evg{ ev };
 
-    if (int rc = dalloc(&b->d_pos, (size_t)num_tris * 9, nullptr)) return rc;
-    if (int rc = dalloc(&b->d_data, (size_t)num_tris * 17, nullptr)) return rc;
     if (int rc = dalloc(&b->d_cells, (size_t)num_cells, nullptr)) return rc;
-    RTC_CU(cudaMemcpyAsync(b->d_pos, positions, (size_t)num_tris * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
-    RTC_CU(cudaMemcpyAsync(b->d_data, data, (size_t)num_tris * sizeof(rtc_tri_data), cudaMemcpyHostToDevice, st));
 
     // initGrid
     int* d_box = nullptr;
@@ -467,7 +589,8 @@ extern "C" int rtc_geometry_build_device(const float* positions, const rtc_tri_d
     RtcDeviceGuard guard(device);
     try {
         rtc::build::Built b;
-        if (int rc = rtc::build::grid_build(positions, data, num_tris, res, nullptr, &b)) return rc;
+        if (int rc = rtc::build::soup_upload(positions, data, num_tris, nullptr, &b)) return rc;
+        if (int rc = rtc::build::grid_build(num_tris, res, nullptr, &b)) return rc;
         std::unique_ptr<RtcGeometryOwner> own(new RtcGeometryOwner());
         own->cells.resize(b.num_cells);
         own->tri_pos.resize(b.num_baked);
@@ -495,6 +618,65 @@ extern "C" int rtc_geometry_build_device(const float* positions, const rtc_tri_d
     }
 }
 
+// The scene around a soup that is already on the device (b.d_pos / b.d_data): grid build, packed layout, bake,
+// materials. Shared by the soup and the glTF entry points.
+static int scene_from_built(rtc_scene* s, rtc::build::Built& b, uint32_t num_tris, const uint32_t res[3],
+                            const rtc_material* materials, uint32_t num_materials, rtc_build_info* info)
+{
+    if (int rc = rtc::build::grid_build(num_tris, res, nullptr, &b)) return rc;
+    rtc::DevScene& d = s->dev;
+    for (int i = 0; i < 3; ++i) {
+        d.bmin[i] = b.grid.bbox_min[i]; d.bmax[i] = b.grid.bbox_max[i];
+        d.res[i] = b.grid.resolution[i]; d.cell[i] = b.grid.cell_size[i];
+    }
+    const size_t nb = rtc_scene_set_packing_(d, res);
+    uint2* d_cells = nullptr; unsigned long long* d_fine = nullptr; uint32_t* d_coarse = nullptr;
+    float4* d_pos = nullptr; uint32_t* d_data = nullptr; uint32_t* d_flag = nullptr;
+    const size_t M = (size_t)b.num_baked;
+    if (int rc = s->alloc(&d_cells, nb * 64)) return rc;
+    if (int rc = s->alloc(&d_fine, nb)) return rc;
+    if (int rc = s->alloc(&d_coarse, (size_t)d.coarse_words)) return rc;
+    if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
+    if (int rc = s->alloc(&d_data, 20 * (size_t)num_tris)) return rc;
+    if (int rc = rtc::build::dalloc(&d_flag, 1, &b.tmp)) return rc;
+    RTC_CU(cudaMemset(d_cells, 0, nb * 64 * sizeof(uint2)));
+    RTC_CU(cudaMemset(d_fine, 0, nb * sizeof(unsigned long long)));
+    RTC_CU(cudaMemset(d_coarse, 0, (size_t)d.coarse_words * sizeof(uint32_t)));
+    RTC_CU(cudaMemset(d_flag, 0, sizeof(uint32_t)));
+    rtc::build::GridP g;
+    rtc::build::Packing pk;
+    for (int a = 0; a < 3; ++a) { g.bmin[a] = b.grid.bbox_min[a]; g.cell[a] = b.grid.cell_size[a]; g.res[a] = res[a]; pk.shift[a] = d.shift[a]; }
+    rtc::build::k_layout<<<(unsigned)((b.num_cells + kThreads - 1) / kThreads), kThreads>>>(b.d_cells, g, pk, d_cells, d_fine, d_coarse);
+    if (M) rtc::build::k_bake_soa<<<(unsigned)((M + kThreads - 1) / kThreads), kThreads>>>(b.d_keys, M, b.d_pos, d_pos, d_pos + M, d_pos + 2 * M);
+    if (num_tris) {
+        const uint64_t words = (uint64_t)num_tris * 20u;
+        rtc::build::k_pack_data<<<(unsigned)((words + kThreads - 1) / kThreads), kThreads>>>(b.d_data, num_tris, num_materials, d_data, d_flag);
+    }
+    RTC_CU(cudaGetLastError());
+    uint32_t flag = 0;
+    RTC_CU(cudaMemcpy(&flag, d_flag, sizeof flag, cudaMemcpyDeviceToHost));
+    if (flag) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "a triangle references a material index >= %u", num_materials);
+    d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse;
+    d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = (const float4*)d_data;
+    s->num_tris = b.num_baked; s->num_src_tris = num_tris;
+    if (info) {
+        info->grid = b.grid; info->num_cells = b.num_cells; info->num_tris = b.num_baked; info->num_src_tris = num_tris;
+        info->empty_cells = b.empty_cells; info->min_tris = b.min_tris; info->max_tris = b.max_tris;
+        info->device_ms = b.device_ms; info->assemble_ms = b.assemble_ms;
+    }
+    if (int rc = rtc_scene_upload_materials_(s, materials, num_materials)) return rc;
+    return rtc_scene_finish_(s);
+}
+
+static int check_res(const uint32_t* res)
+{
+    if (!res || !res[0] || !res[1] || !res[2]) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "zero grid resolution");
+    for (int a = 0; a < 3; ++a)
+        if (res[a] > rtc::kMaxGridRes)
+            return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)", res[a], a, rtc::kMaxGridRes);
+    return RTC_OK;
+}
+
 extern "C" int rtc_scene_create_from_soup(const float* positions, const rtc_tri_data* data, uint32_t num_tris,
                                           const uint32_t res[3], const rtc_material* materials, uint32_t num_materials,
                                           int device, rtc_scene** out, rtc_build_info* info)
@@ -503,62 +685,84 @@ extern "C" int rtc_scene_create_from_soup(const float* positions, const rtc_tri_
     *out = nullptr;
     if (info) memset(info, 0, sizeof *info);
     if (int rc = check_soup_args(positions, data, num_tris, res)) return rc;
-    for (int a = 0; a < 3; ++a)
-        if (res[a] > rtc::kMaxGridRes)
-            return rtc_fail_(RTC_ERR_UNSUPPORTED, "grid resolution %u on axis %d exceeds %u (cell coordinates are packed 10 bits per axis)", res[a], a, rtc::kMaxGridRes);
+    if (int rc = check_res(res)) return rc;
     rtc_scene* s = nullptr;
     if (int rc = rtc_scene_new_(device, &s)) return rc;
     RtcDeviceGuard guard(s->device);
     const auto t0 = std::chrono::steady_clock::now();
     auto body = [&]() -> int {
         rtc::build::Built b;
-        if (int rc = rtc::build::grid_build(positions, data, num_tris, res, nullptr, &b)) return rc;
-        rtc::DevScene& d = s->dev;
-        for (int i = 0; i < 3; ++i) {
-            d.bmin[i] = b.grid.bbox_min[i]; d.bmax[i] = b.grid.bbox_max[i];
-            d.res[i] = b.grid.resolution[i]; d.cell[i] = b.grid.cell_size[i];
-        }
-        const size_t nb = rtc_scene_set_packing_(d, res);
-        uint2* d_cells = nullptr; unsigned long long* d_fine = nullptr; uint32_t* d_coarse = nullptr;
-        float4* d_pos = nullptr; uint32_t* d_data = nullptr; uint32_t* d_flag = nullptr;
-        const size_t M = (size_t)b.num_baked;
-        if (int rc = s->alloc(&d_cells, nb * 64)) return rc;
-        if (int rc = s->alloc(&d_fine, nb)) return rc;
-        if (int rc = s->alloc(&d_coarse, (size_t)d.coarse_words)) return rc;
-        if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
-        if (int rc = s->alloc(&d_data, 20 * (size_t)num_tris)) return rc;
-        if (int rc = rtc::build::dalloc(&d_flag, 1, &b.tmp)) return rc;
-        RTC_CU(cudaMemset(d_cells, 0, nb * 64 * sizeof(uint2)));
-        RTC_CU(cudaMemset(d_fine, 0, nb * sizeof(unsigned long long)));
-        RTC_CU(cudaMemset(d_coarse, 0, (size_t)d.coarse_words * sizeof(uint32_t)));
-        RTC_CU(cudaMemset(d_flag, 0, sizeof(uint32_t)));
-        rtc::build::GridP g;
-        rtc::build::Packing pk;
-        for (int a = 0; a < 3; ++a) { g.bmin[a] = b.grid.bbox_min[a]; g.cell[a] = b.grid.cell_size[a]; g.res[a] = res[a]; pk.shift[a] = d.shift[a]; }
-        rtc::build::k_layout<<<(unsigned)((b.num_cells + kThreads - 1) / kThreads), kThreads>>>(b.d_cells, g, pk, d_cells, d_fine, d_coarse);
-        if (M) rtc::build::k_bake_soa<<<(unsigned)((M + kThreads - 1) / kThreads), kThreads>>>(b.d_keys, M, b.d_pos, d_pos, d_pos + M, d_pos + 2 * M);
-        if (num_tris) {
-            const uint64_t words = (uint64_t)num_tris * 20u;
-            rtc::build::k_pack_data<<<(unsigned)((words + kThreads - 1) / kThreads), kThreads>>>(b.d_data, num_tris, num_materials, d_data, d_flag);
-        }
-        RTC_CU(cudaGetLastError());
-        uint32_t flag = 0;
-        RTC_CU(cudaMemcpy(&flag, d_flag, sizeof flag, cudaMemcpyDeviceToHost));
-        if (flag) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "a triangle references a material index >= %u", num_materials);
-        d.cells = d_cells; d.fine = d_fine; d.coarse = d_coarse;
-        d.tri_v0 = d_pos; d.tri_e1 = d_pos + M; d.tri_e2 = d_pos + 2 * M; d.tri_data = (const float4*)d_data;
-        s->num_tris = b.num_baked; s->num_src_tris = num_tris;
-        if (info) {
-            info->grid = b.grid; info->num_cells = b.num_cells; info->num_tris = b.num_baked; info->num_src_tris = num_tris;
-            info->empty_cells = b.empty_cells; info->min_tris = b.min_tris; info->max_tris = b.max_tris;
-            info->device_ms = b.device_ms;
-        }
-        if (int rc = rtc_scene_upload_materials_(s, materials, num_materials)) return rc;
-        return rtc_scene_finish_(s);
+        if (int rc = rtc::build::soup_upload(positions, data, num_tris, nullptr, &b)) return rc;
+        return scene_from_built(s, b, num_tris, res, materials, num_materials, info);
     };
     const int rc = body();
     if (rc != RTC_OK) { rtc_keep_error_free_(s); return rc; }
     if (info) info->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
     return RTC_OK;
+}
+
+// ---- stage1's triangle assembly on the device ---------------------------------------------
+
+extern "C" int rtc_scene_create_from_gltf(const char* path, const char* camera_name, uint32_t width, uint32_t height,
+                                          int num_threads, const uint32_t res[3], int device,
+                                          rtc_scene** out, rtc_camera* camera, rtc_build_info* info)
+{
+    if (!out || !path) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_create_from_gltf: null argument");
+    *out = nullptr;
+    if (info) memset(info, 0, sizeof *info);
+    if (int rc = check_res(res)) return rc;
+    const auto t0 = std::chrono::steady_clock::now();
+    try {
+        RtcGltfPlan plan;
+        if (int rc = rtc_gltf_plan_(path, camera_name, width, height, num_threads, &plan)) return rc;
+        rtc_scene* s = nullptr;
+        if (int rc = rtc_scene_new_(device, &s)) return rc;
+        RtcDeviceGuard guard(s->device);
+        auto body = [&]() -> int {
+            rtc::build::Built b;
+            if (int rc = rtc::build::soup_assemble(plan, nullptr, &b)) return rc;
+            return scene_from_built(s, b, plan.num_tris, res, plan.materials.data(), (uint32_t)plan.materials.size(), info);
+        };
+        const int rc = body();
+        if (rc != RTC_OK) { rtc_keep_error_free_(s); return rc; }
+        if (camera) *camera = plan.camera;
+        if (info) info->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        *out = s;
+        return RTC_OK;
+    } catch (const std::bad_alloc&) {
+        return rtc_fail_(RTC_ERR_OUT_OF_MEMORY, "rtc_scene_create_from_gltf: host allocation failed");
+    }
+}
+
+extern "C" int rtc_gltf_load_device(const char* path, const char* camera_name, uint32_t width, uint32_t height,
+                                    int num_threads, int device, rtc_host_scene* out)
+{
+    if (!out || !path) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "rtc_gltf_load_device: null argument");
+    memset(out, 0, sizeof *out);
+    try {
+        RtcGltfPlan plan;
+        if (int rc = rtc_gltf_plan_(path, camera_name, width, height, num_threads, &plan)) return rc;
+        if (int rc = pick_device(&device)) return rc;
+        RtcDeviceGuard guard(device);
+        rtc::build::Built b;
+        if (int rc = rtc::build::soup_assemble(plan, nullptr, &b)) return rc;
+        std::unique_ptr<RtcHostSceneOwner> own(new RtcHostSceneOwner());
+        own->positions.resize((size_t)plan.num_tris * 9);
+        own->tri_data.resize(plan.num_tris);
+        if (plan.num_tris) {
+            RTC_CU(cudaMemcpy(own->positions.data(), b.d_pos, own->positions.size() * sizeof(float), cudaMemcpyDeviceToHost));
+            RTC_CU(cudaMemcpy(own->tri_data.data(), b.d_data, own->tri_data.size() * sizeof(rtc_tri_data), cudaMemcpyDeviceToHost));
+        }
+        own->materials = std::move(plan.materials);
+        own->texels = std::move(plan.texels);
+        out->camera = plan.camera;
+        out->positions = own->positions.data(); out->tri_data = own->tri_data.data(); out->num_tris = plan.num_tris;
+        out->materials = own->materials.data(); out->num_materials = (uint32_t)own->materials.size();
+        out->num_images = plan.num_images;
+        out->owner = own.release();
+        return RTC_OK;
+    } catch (const std::bad_alloc&) {
+        return rtc_fail_(RTC_ERR_OUT_OF_MEMORY, "rtc_gltf_load_device: host allocation failed");
+    }
 }

@@ -116,51 +116,65 @@ int main(int argc, char** argv)
     if (num_threads < 1) num_threads = 1;
     fprintf(stderr, "info: Num threads: %d\n", num_threads);
 
-    // stage1: Loaded (files + image decode) and Preprocessed (camera, materials, triangles) are one call here
-    Clock::time_point t = Clock::now();
-    rtc_host_scene host;
-    if (rtc_gltf_load(args.in.c_str(), args.has_camera ? args.camera.c_str() : nullptr, args.width, args.height,
-                      num_threads, &host) != RTC_OK)
-        return die(args.in.c_str());
-    fprintf(stderr, "info: Pixels count: %u\n", host.camera.w * host.camera.h);
-    fprintf(stderr, "info: Materials count: %u\n", host.num_materials);
-    fprintf(stderr, "info: Loaded in %s\n", since(t).c_str());
-    fprintf(stderr, "info: Preprocessed in 0ns (camera, materials and triangles are part of the load call above)\n");
-
-    // stage2: Geometry.build + bakeInto, then the upload that stands where the Zig scene arena is filled
-    t = Clock::now();
-    // The grid is built and baked on the device (rtc_scene_create_from_soup); RTC_HOST_BUILD=1 keeps the
-    // host-thread build + upload of the baked arrays (same scene bit for bit).
     fprintf(stderr, "info: Grid resolution: { %u, %u, %u }\n", config.grid_resolution[0], config.grid_resolution[1], config.grid_resolution[2]);
+    const char* camera_name = args.has_camera ? args.camera.c_str() : nullptr;
+    const char* env_load = getenv("RTC_HOST_LOAD");
+    const char* env_build = getenv("RTC_HOST_BUILD");
+    const bool host_build = env_build && env_build[0] == '1';
+    const bool host_load = host_build || (env_load && env_load[0] == '1');
+    Clock::time_point t = Clock::now();
     rtc_scene* scene = nullptr;
+    rtc_camera camera;
     rtc_build_info bi;
     memset(&bi, 0, sizeof bi);
-    const char* host_build = getenv("RTC_HOST_BUILD");
-    if (host_build && host_build[0] == '1') {
-        rtc_geometry geo;
-        if (rtc_geometry_build(host.positions, host.tri_data, host.num_tris, config.grid_resolution, &geo) != RTC_OK) return die("grid build");
-        bi.grid = geo.grid; bi.num_cells = geo.num_cells; bi.num_tris = geo.num_tris; bi.num_src_tris = geo.num_src_tris;
-        bi.empty_cells = geo.empty_cells; bi.min_tris = geo.min_tris; bi.max_tris = geo.max_tris;
-        rtc_scene_desc desc;
-        memset(&desc, 0, sizeof desc);
-        desc.grid = geo.grid; desc.cells = geo.cells; desc.num_cells = geo.num_cells;
-        desc.tri_pos = geo.tri_pos; desc.tri_data = geo.tri_data; desc.num_tris = geo.num_tris;
-        desc.materials = host.materials; desc.num_materials = host.num_materials; desc.num_src_tris = geo.num_src_tris;
-        if (rtc_scene_create(&desc, args.device, &scene) != RTC_OK) return die("scene upload");
-        rtc_geometry_free(&geo);
+    memset(&camera, 0, sizeof camera);
+    if (!host_load) {
+        // Default: files + image decode on host threads, then triangle assembly (stage1), grid build and bake
+        // (stage2) on the device in one call; the soup and the baked arrays never exist on the host.
+        if (rtc_scene_create_from_gltf(args.in.c_str(), camera_name, args.width, args.height, num_threads, config.grid_resolution,
+                                       args.device, &scene, &camera, &bi) != RTC_OK)
+            return die(args.in.c_str());
+        fprintf(stderr, "info: Pixels count: %u\n", camera.w * camera.h);
+        fprintf(stderr, "info: Loaded, preprocessed and compiled in %s (device: triangle assembly %.3fms, grid build %.3fms)\n", since(t).c_str(),
+                (double)bi.assemble_ms, (double)bi.device_ms);
     } else {
-        if (rtc_scene_create_from_soup(host.positions, host.tri_data, host.num_tris, config.grid_resolution, host.materials,
-                                       host.num_materials, args.device, &scene, &bi) != RTC_OK)
-            return die("grid build");
+        // RTC_HOST_LOAD=1: stage1 on host threads, the grid built and baked on the device from the uploaded soup.
+        // RTC_HOST_BUILD=1: stage2 on a host thread too, the baked arrays uploaded. Same scene bit for bit.
+        rtc_host_scene host;
+        if (rtc_gltf_load(args.in.c_str(), camera_name, args.width, args.height, num_threads, &host) != RTC_OK) return die(args.in.c_str());
+        camera = host.camera;
+        fprintf(stderr, "info: Pixels count: %u\n", camera.w * camera.h);
+        fprintf(stderr, "info: Materials count: %u\n", host.num_materials);
+        fprintf(stderr, "info: Loaded in %s\n", since(t).c_str());
+        fprintf(stderr, "info: Preprocessed in 0ns (camera, materials and triangles are part of the load call above)\n");
+        t = Clock::now();
+        if (host_build) {
+            rtc_geometry geo;
+            if (rtc_geometry_build(host.positions, host.tri_data, host.num_tris, config.grid_resolution, &geo) != RTC_OK) return die("grid build");
+            bi.grid = geo.grid; bi.num_cells = geo.num_cells; bi.num_tris = geo.num_tris; bi.num_src_tris = geo.num_src_tris;
+            bi.empty_cells = geo.empty_cells; bi.min_tris = geo.min_tris; bi.max_tris = geo.max_tris;
+            rtc_scene_desc desc;
+            memset(&desc, 0, sizeof desc);
+            desc.grid = geo.grid; desc.cells = geo.cells; desc.num_cells = geo.num_cells;
+            desc.tri_pos = geo.tri_pos; desc.tri_data = geo.tri_data; desc.num_tris = geo.num_tris;
+            desc.materials = host.materials; desc.num_materials = host.num_materials; desc.num_src_tris = geo.num_src_tris;
+            if (rtc_scene_create(&desc, args.device, &scene) != RTC_OK) return die("scene upload");
+            rtc_geometry_free(&geo);
+        } else {
+            if (rtc_scene_create_from_soup(host.positions, host.tri_data, host.num_tris, config.grid_resolution, host.materials,
+                                           host.num_materials, args.device, &scene, &bi) != RTC_OK)
+                return die("grid build");
+        }
+        rtc_host_scene_free(&host);
+        fprintf(stderr, "info: Compiled in %s\n", since(t).c_str());
     }
     fprintf(stderr, "info: Empty cells: %u/%llu (%.2f%%) min triangles: %u max triangles: %u mean_triangles: %llu\n", bi.empty_cells,
             (unsigned long long)bi.num_cells, bi.num_cells ? 100.0 * bi.empty_cells / (double)bi.num_cells : 0.0, bi.min_tris, bi.max_tris,
             (unsigned long long)(bi.num_cells > bi.empty_cells ? bi.num_tris / (bi.num_cells - bi.empty_cells) : 0));
     fprintf(stderr, "info: Unique triangle count: %u/%llu (%.2f%%)\n", bi.num_src_tris, (unsigned long long)bi.num_tris,
             bi.num_tris ? 100.0 * bi.num_src_tris / (double)bi.num_tris : 0.0);
-    fprintf(stderr, "info: Compiled in %s\n", since(t).c_str());
 
-    std::vector<uint8_t> img((size_t)host.camera.w * host.camera.h * 3);
+    std::vector<uint8_t> img((size_t)camera.w * camera.h * 3);
     t = Clock::now();
     rtc_params prm;
     memset(&prm, 0, sizeof prm);
@@ -171,17 +185,16 @@ int main(int argc, char** argv)
     rtc_aux aux;
     memset(&aux, 0, sizeof aux);
     aux.stats = &stats;
-    if (rtc_render(scene, &host.camera, &prm, img.data(), &aux) != RTC_OK) return die("render");
+    if (rtc_render(scene, &camera, &prm, img.data(), &aux) != RTC_OK) return die("render");
     const double render_s = std::chrono::duration<double>(Clock::now() - t).count();
     fprintf(stderr, "info: Rendered in %s\n", since(t).c_str());
     fprintf(stderr, "info: Rays: %llu (%.1f Mrays/s), paths: %llu, kernels launched: %llu\n", (unsigned long long)stats.rays,
             render_s > 0 ? (double)stats.rays / render_s / 1e6 : 0.0, (unsigned long long)stats.paths, (unsigned long long)stats.launches);
 
     t = Clock::now();
-    if (rtc_png_write(args.out.c_str(), host.camera.w, host.camera.h, img.data()) != RTC_OK) return die("WritePngFail");
+    if (rtc_png_write(args.out.c_str(), camera.w, camera.h, img.data()) != RTC_OK) return die("WritePngFail");
     fprintf(stderr, "info: Saved in %s\n", since(t).c_str());
     rtc_scene_destroy(scene);
-    rtc_host_scene_free(&host);
     fprintf(stderr, "info: Done in %s\n", since(start).c_str());
     return 0;
 }

@@ -8,6 +8,7 @@
 // Host code only; compiled with -ffp-contract=off because the transform arithmetic decides the bits of every
 // vertex the render path sees, and must evaluate like the reference's fp32 code.
 #include "../../include/rtc.h"
+#include "rtc_gltf_plan.h"
 #include "rtc_json.h"
 #include "rtc_png.h"
 
@@ -324,6 +325,7 @@ struct Accessor {
     const uint8_t* base = nullptr;
     size_t count = 0, stride = 0;
     int component = 0;
+    size_t buffer = 0, offset = 0;      // where base lies: buffers[buffer] + offset
 };
 Accessor accessor(const Asset& a, long long idx, const char* want_type, bool want_float)
 {
@@ -350,6 +352,8 @@ Accessor accessor(const Asset& a, long long idx, const char* want_type, bool wan
     if (r.stride == 0) r.stride = comp_size * ncomp;
     if (r.count && off + (r.count - 1) * r.stride + comp_size * ncomp > bytes.n) fail(RTC_ERR_FORMAT, "glTF: accessor outside its bufferView");
     r.base = bytes.p + off;
+    r.buffer = (size_t)view.integer("buffer", -1);
+    r.offset = (size_t)view.integer("byteOffset", 0) + off;
     return r;
 }
 inline V3 read_v3(const Accessor& a, size_t i) { float f[3]; memcpy(f, a.base + i * a.stride, 12); return v3(f[0], f[1], f[2]); }
@@ -361,15 +365,12 @@ inline uint32_t read_index(const Accessor& a, size_t i)
     return *p;
 }
 
-struct HostScene {
-    std::vector<float> positions;
-    std::vector<rtc_tri_data> tri_data;
-    std::vector<rtc_material> materials;
-    std::vector<std::vector<float>> texels;      // owners of rtc_texture.texels
-};
+using HostScene = RtcHostSceneOwner;      // rtc_gltf_plan.h
 
 // loadTriangles (src/stage1.zig:217-259): for every node with a mesh, for every primitive, in file order.
-void load_geometry(const Asset& a, HostScene& out)
+// f(matrix, material, pos, nrm, uv, has_uv, ind) sees every primitive once, validated.
+template <typename F>
+void for_each_primitive(const Asset& a, F&& f)
 {
     const Json& nodes = arr_of(a.doc, "nodes");
     const size_t num_materials = arr_of(a.doc, "materials").arr.size();
@@ -391,25 +392,71 @@ void load_geometry(const Asset& a, HostScene& out)
             const bool has_uv = attrs.has("TEXCOORD_0");
             if (has_uv) uv = accessor(a, attrs.integer("TEXCOORD_0", -1), "VEC2", true);
             const Accessor ind = accessor(a, prim.integer("indices", -1), "SCALAR", false);
-            const size_t tris = ind.count / 3;
-            for (size_t t = 0; t < tris; ++t) {
-                rtc_tri_data d;
-                memset(&d, 0, sizeof d);
-                d.material = (uint32_t)material;
-                d.src_tri = (uint32_t)out.tri_data.size();
-                for (int i = 0; i < 3; ++i) {
-                    const uint32_t v = read_index(ind, t * 3 + (size_t)i);
-                    if (v >= pos.count || v >= nrm.count || (has_uv && v >= uv.count)) fail(RTC_ERR_FORMAT, "glTF: vertex index out of range");
-                    const V3 p = transform_position(matrix, read_v3(pos, v));
-                    const V3 nn = normalize(transform_direction(matrix, read_v3(nrm, v)));     // not the inverse transpose (TODO in the reference)
-                    out.positions.push_back(p.x); out.positions.push_back(p.y); out.positions.push_back(p.z);
-                    d.normal[i][0] = nn.x; d.normal[i][1] = nn.y; d.normal[i][2] = nn.z;
-                    if (has_uv) memcpy(d.texcoord[i], uv.base + v * uv.stride, 8);
-                }
-                out.tri_data.push_back(d);
-            }
+            f(matrix, (uint32_t)material, pos, nrm, uv, has_uv, ind);
         }
     }
+}
+
+void load_geometry(const Asset& a, HostScene& out)
+{
+    for_each_primitive(a, [&](const Mat4& matrix, uint32_t material, const Accessor& pos, const Accessor& nrm,
+                              const Accessor& uv, bool has_uv, const Accessor& ind) {
+        const size_t tris = ind.count / 3;
+        for (size_t t = 0; t < tris; ++t) {
+            rtc_tri_data d;
+            memset(&d, 0, sizeof d);
+            d.material = material;
+            d.src_tri = (uint32_t)out.tri_data.size();
+            for (int i = 0; i < 3; ++i) {
+                const uint32_t v = read_index(ind, t * 3 + (size_t)i);
+                if (v >= pos.count || v >= nrm.count || (has_uv && v >= uv.count)) fail(RTC_ERR_FORMAT, "glTF: vertex index out of range");
+                const V3 p = transform_position(matrix, read_v3(pos, v));
+                const V3 nn = normalize(transform_direction(matrix, read_v3(nrm, v)));     // not the inverse transpose (TODO in the reference)
+                out.positions.push_back(p.x); out.positions.push_back(p.y); out.positions.push_back(p.z);
+                d.normal[i][0] = nn.x; d.normal[i][1] = nn.y; d.normal[i][2] = nn.z;
+                if (has_uv) memcpy(d.texcoord[i], uv.base + v * uv.stride, 8);
+            }
+            out.tri_data.push_back(d);
+        }
+    });
+}
+
+// The same walk with the per-triangle loop left to the device (rtc_build.cu: k_assemble): one table row per
+// primitive, the buffers the rows point into laid out back to back (256-byte aligned) in one blob.
+void plan_geometry(const Asset& a, RtcGltfPlan& out)
+{
+    out.buffer_base.assign(a.buffers.size(), ~(uint64_t)0);
+    uint64_t total = 0;
+    auto place = [&](const Accessor& acc) -> uint64_t {
+        uint64_t& base = out.buffer_base[acc.buffer];
+        if (base == ~(uint64_t)0) { base = out.blob_bytes; out.blob_bytes += (a.buffers[acc.buffer].size() + 255u) & ~(uint64_t)255u; }
+        return base + acc.offset;
+    };
+    auto u32 = [](size_t v, const char* what) -> uint32_t {
+        if (v > 0xFFFFFFFFull) fail(RTC_ERR_UNSUPPORTED, std::string("glTF: ") + what + " does not fit 32 bits");
+        return (uint32_t)v;
+    };
+    for_each_primitive(a, [&](const Mat4& matrix, uint32_t material, const Accessor& pos, const Accessor& nrm,
+                              const Accessor& uv, bool has_uv, const Accessor& ind) {
+        const size_t tris = ind.count / 3;
+        if (!tris) return;
+        RtcPrimRef r;
+        memset(&r, 0, sizeof r);
+        for (int c = 0; c < 4; ++c)
+            for (int row = 0; row < 4; ++row) r.m[c * 4 + row] = matrix.m[c][row];
+        r.off_pos = place(pos); r.stride_pos = u32(pos.stride, "byteStride"); r.count_pos = u32(pos.count, "accessor.count");
+        r.off_nrm = place(nrm); r.stride_nrm = u32(nrm.stride, "byteStride"); r.count_nrm = u32(nrm.count, "accessor.count");
+        if (has_uv) { r.off_uv = place(uv); r.stride_uv = u32(uv.stride, "byteStride"); r.count_uv = u32(uv.count, "accessor.count"); }
+        r.off_ind = place(ind); r.stride_ind = u32(ind.stride, "byteStride");
+        r.index_component = (uint32_t)ind.component;
+        r.has_uv = has_uv ? 1u : 0u;
+        r.material = material;
+        if (total + tris > 0xFFFFFFFFull) fail(RTC_ERR_UNSUPPORTED, "glTF: more than 2^32 - 1 triangles");
+        r.first_tri = (uint32_t)total; r.num_tris = (uint32_t)tris;
+        total += tris;
+        out.prims.push_back(r);
+    });
+    out.num_tris = (uint32_t)total;
 }
 
 // loadCamera (src/stage1.zig:282-371).
@@ -567,6 +614,24 @@ int guarded(F&& f)
 }
 
 }  // namespace
+
+// rtc_gltf_plan.h
+int rtc_gltf_plan_(const char* path, const char* camera_name, uint32_t width, uint32_t height, int num_threads,
+                   RtcGltfPlan* out)
+{
+    return guarded([&] {
+        Asset a;
+        load_asset(path, num_threads, a);
+        HostScene hs;
+        load_camera(a, camera_name, width, height, &out->camera);     // order of src/main.zig:109-112
+        load_materials(a, hs);
+        plan_geometry(a, *out);
+        out->materials = std::move(hs.materials);
+        out->texels = std::move(hs.texels);          // moving the outer vector keeps the inner data() pointers
+        out->num_images = (uint32_t)a.images.size();
+        out->buffers = std::move(a.buffers);
+    });
+}
 
 extern "C" {
 

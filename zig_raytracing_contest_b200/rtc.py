@@ -59,6 +59,9 @@ def lib():
     L.rtc_geometry_free.restype = None
     L.rtc_config_load.argtypes = [C.c_char_p, C.POINTER(abi.Config)]
     L.rtc_gltf_load.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(abi.HostScene)]
+    L.rtc_gltf_load_device.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(abi.HostScene)]
+    L.rtc_scene_create_from_gltf.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_int,
+                                             C.POINTER(C.c_void_p), C.POINTER(abi.Camera), C.POINTER(abi.BuildInfo)]
     L.rtc_host_scene_free.argtypes = [C.POINTER(abi.HostScene)]
     L.rtc_host_scene_free.restype = None
     L.rtc_png_write.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p]
@@ -89,12 +92,18 @@ def load_config(path="config.json"):
 
 class HostSceneData:
     """What stage1 leaves in memory (src/main.zig:104-112), copied out of rtc_gltf_load into numpy:
-    camera (abi.Camera), positions [N,3,3], tri_data [N] (TRI_DATA_DTYPE), materials [MaterialData]."""
+    camera (abi.Camera), positions [N,3,3], tri_data [N] (TRI_DATA_DTYPE), materials [MaterialData].
+    device=None: the host loader; device=k (-1 = current): the triangles are assembled on that GPU
+    (rtc_gltf_load_device), bit-identical results."""
 
-    def __init__(self, path, camera=None, width=None, height=None, num_threads=1):
+    def __init__(self, path, camera=None, width=None, height=None, num_threads=1, device=None):
         hs = abi.HostScene()
-        _check(lib().rtc_gltf_load(os.fsencode(path), camera.encode() if camera is not None else None,
-                                   int(width or 0), int(height or 0), int(num_threads), C.byref(hs)))
+        cam = camera.encode() if camera is not None else None
+        if device is None:
+            _check(lib().rtc_gltf_load(os.fsencode(path), cam, int(width or 0), int(height or 0), int(num_threads), C.byref(hs)))
+        else:
+            _check(lib().rtc_gltf_load_device(os.fsencode(path), cam, int(width or 0), int(height or 0), int(num_threads),
+                                              int(device), C.byref(hs)))
         try:
             n = int(hs.num_tris)
             self.camera = abi.Camera.from_buffer_copy(hs.camera)
@@ -276,6 +285,22 @@ class Scene:
                                                 C.c_uint32(positions.shape[0]), C.c_void_p(res.ctypes.data),
                                                 mats, C.c_uint32(len(materials)), C.c_int(device),
                                                 C.byref(self._h), C.byref(self.build_info)))
+        return self
+
+    @classmethod
+    def from_gltf(cls, path, resolution, camera=None, width=None, height=None, num_threads=1, device=-1):
+        """loadGltfFile .. bakeInto (src/main.zig:104-118) in one call, triangle assembly and grid build on the
+        device (rtc_scene_create_from_gltf). Sets `camera` (abi.Camera) and `build_info`."""
+        res = np.ascontiguousarray(resolution, dtype=np.uint32)
+        self = cls.__new__(cls)
+        self.desc, self._keep = None, None
+        self._h = C.c_void_p()
+        self.build_info = abi.BuildInfo()
+        self.camera = abi.Camera()
+        _check(lib().rtc_scene_create_from_gltf(os.fsencode(path), camera.encode() if camera is not None else None,
+                                                int(width or 0), int(height or 0), int(num_threads),
+                                                C.c_void_p(res.ctypes.data), C.c_int(device),
+                                                C.byref(self._h), C.byref(self.camera), C.byref(self.build_info)))
         return self
 
     def close(self):
