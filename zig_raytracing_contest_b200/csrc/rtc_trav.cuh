@@ -145,22 +145,31 @@ RTC_HD void trav_commit(Trav& s, const TravStep& o)
 // — smaller value, or equal value and higher priority (z over y over x) — and move the cell accordingly.
 RTC_HD void trav_enter_axis(float& t, float d, uint32_t& c, uint32_t shift, float T, bool tie_wins)
 {
+    const bool neg = (int32_t)f_bits(d) < 0;
     const uint32_t lo = (c >> shift) & 3u;
-    const uint32_t r = trav_inner(lo, d);
+    const uint32_t r = neg ? lo : 3u - lo;                          // trav_inner
     const float a = fabsf(d);
     const float c0 = t, c1 = c0 + a, c2 = c1 + a, c3 = c2 + a;
-    const bool p0 = r >= 1u && (tie_wins ? c0 <= T : c0 < T);
-    const bool p1 = p0 && r >= 2u && (tie_wins ? c1 <= T : c1 < T);
-    const bool p2 = p1 && r == 3u && (tie_wins ? c2 <= T : c2 < T);
-    const uint32_t k = (p0 ? 1u : 0u) + (p1 ? 1u : 0u) + (p2 ? 1u : 0u);
-    t = p2 ? c3 : (p1 ? c2 : (p0 ? c1 : c0));
-    c = (int32_t)f_bits(d) < 0 ? c - (k << shift) : c + (k << shift);
+    // the values only grow, so the crossings that come before (T, axis) are a prefix: count it, capped by r
+    const uint32_t n = ((c0 < T || (tie_wins && c0 == T)) ? 1u : 0u) + ((c1 < T || (tie_wins && c1 == T)) ? 1u : 0u) +
+                       ((c2 < T || (tie_wins && c2 == T)) ? 1u : 0u);
+    const uint32_t k = n < r ? n : r;
+    t = k == 0u ? c0 : (k == 1u ? c1 : (k == 2u ? c2 : c3));
+    const uint32_t dk = k << shift;
+    c = neg ? c - dk : c + dk;
 }
+// The two axes other than `axis`, picked with selects so that the arithmetic exists once per axis slot:
+//   axis x: (y, wins ties against x), (z, wins);   axis y: (x, loses), (z, wins);   axis z: (x, loses), (y, loses)
 RTC_HD void trav_enter(Trav& s, float T, uint32_t axis)
 {
-    if (axis != 0u) trav_enter_axis(s.tx, s.dx, s.c, 0u, T, false);            // x never wins a tie
-    if (axis != 1u) trav_enter_axis(s.ty, s.dy, s.c, 2u, T, axis == 0u);       // y wins against x
-    if (axis != 2u) trav_enter_axis(s.tz, s.dz, s.c, 4u, T, true);             // z wins against x and y
+    const bool a0 = axis == 0u, a2 = axis == 2u;
+    float tA = a0 ? s.ty : s.tx, tB = a2 ? s.ty : s.tz;
+    const float dA = a0 ? s.dy : s.dx, dB = a2 ? s.dy : s.dz;
+    trav_enter_axis(tA, dA, s.c, a0 ? 2u : 0u, T, a0);
+    trav_enter_axis(tB, dB, s.c, a2 ? 2u : 4u, T, !a2);
+    s.tx = a0 ? s.tx : tA;
+    s.ty = a0 ? tA : (a2 ? tB : s.ty);
+    s.tz = a2 ? s.tz : tB;
 }
 
 // One iteration of the walk for a ray standing in a cell it has finished with (empty, or its triangles tested):
