@@ -246,7 +246,7 @@ typedef struct rtc_build_info {
     uint32_t empty_cells;
     uint32_t min_tris, max_tris;
     float    device_ms;      /* CUDA-event time of the grid-build kernels (bbox, binning, scan, sort)         */
-    float    assemble_ms;    /* CUDA-event time of the triangle assembly (rtc_scene_create_from_gltf), else 0  */
+    float    assemble_ms;    /* CUDA-event time of triangle assembly + texel linearisation (rtc_scene_create_from_gltf), else 0 */
     double   total_ms;       /* wall time of the whole call: upload + build + bake + textures    */
 } rtc_build_info;
 
@@ -295,8 +295,9 @@ void rtc_host_scene_free(rtc_host_scene* scene);
 
 /* The same stage1 with loadTriangles' per-triangle loop (src/stage1.zig:235-255: index fetch, node transform
  * of positions and normals, normalize, texcoords) ON the device: the file's buffers and one table row per
- * primitive are uploaded, one sm_100a kernel writes the soup. Needs a GPU; results are bit-identical to
- * rtc_gltf_load's (an out-of-range vertex index is the same RTC_ERR_FORMAT).
+ * primitive are uploaded, one sm_100a kernel writes the soup; texture images go up as decoded 8-bit RGBA and are
+ * linearised there (stb's pow(c/255, 2.2) table times the material factor, MASK / BLEND alpha; src/stage1.zig:427-472).
+ * Needs a GPU; results are bit-identical to rtc_gltf_load's (an out-of-range vertex index is the same RTC_ERR_FORMAT).
  *
  * rtc_scene_create_from_gltf = loadGltfFile .. bakeInto (src/main.zig:104-118) in one call: the soup never
  * exists on the host, the grid is built and baked on the device from it (as rtc_scene_create_from_soup), and

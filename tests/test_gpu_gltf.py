@@ -29,14 +29,17 @@ def _same_host_scene(a, b):
             assert (ta.u_min, ta.u_max, ta.v_min, ta.v_max) == (tb.u_min, tb.u_max, tb.v_min, tb.v_max)
 
 
+@pytest.mark.parametrize("scene", ["atrium", "cornell"])
 @pytest.mark.parametrize("flavour", ["gltf", "glb", "embed"])
-def test_device_assembly_matches_host_loader(tmp_path, flavour):
-    spec = scenes.atrium(detail=0.3)
+def test_device_assembly_matches_host_loader(tmp_path, flavour, scene):
+    """Triangles AND texels (device linearisation: colour * factor, MASK / BLEND alpha) against the host loader."""
+    spec = scenes.atrium(detail=0.3) if scene == "atrium" else scenes.cornell(subdiv=6)
     path = str(tmp_path / ("scene.glb" if flavour == "glb" else "scene.gltf"))
     gltf_io.write_gltf(spec, path, node_translation=(0.25, -0.5, 1.0), node_scale=2.0, glb=flavour == "glb", embed=flavour == "embed")
     host = rtc.HostSceneData(path, camera="Camera 1", height=72, num_threads=3)
     dev = rtc.HostSceneData(path, camera="Camera 1", height=72, num_threads=3, device=0)
-    assert len(host.positions) == len(spec.positions) > 1000
+    assert len(host.positions) == len(spec.positions) > 400
+    assert any(m.base_color.texels.shape[0] > 1 for m in host.materials) and any(m.transparency.texels.shape[0] > 1 for m in host.materials)
     _same_host_scene(host, dev)
 
 

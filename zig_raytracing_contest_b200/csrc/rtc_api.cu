@@ -66,14 +66,15 @@ int rtc_device_count(void)
 namespace {
 
 int upload_texture(rtc_scene* s, const rtc_texture& t, int want_channels, rtc::DevTexture* out,
-                   std::vector<std::pair<const float*, void*>>& seen)
+                   std::vector<std::pair<const float*, void*>>& seen, const void* preset)
 {
-    if (!t.texels || t.w <= 0 || t.h <= 0) return fail(RTC_ERR_INVALID_ARGUMENT, "texture without texels or with non-positive size");
+    if ((!t.texels && !preset) || t.w <= 0 || t.h <= 0) return fail(RTC_ERR_INVALID_ARGUMENT, "texture without texels or with non-positive size");
     if (t.channels != want_channels) return fail(RTC_ERR_INVALID_ARGUMENT, "texture has %d channels, expected %d", t.channels, want_channels);
     if ((int64_t)t.w * t.h > (int64_t)1 << 30) return fail(RTC_ERR_UNSUPPORTED, "texture larger than 2^30 texels");
     out->w = t.w; out->h = t.h;
     out->u_min = t.u_min; out->u_max = t.u_max; out->v_min = t.v_min; out->v_max = t.v_max;
     out->wf = (float)t.w; out->hf = (float)t.h;            // Texture.w/h: f32 (src/stage3.zig:85-86)
+    if (preset) { out->texels = preset; return RTC_OK; }   // already on the device, in the device layout
     for (auto& kv : seen)
         if (kv.first == t.texels) { out->texels = kv.second; return RTC_OK; }
     const size_t n = (size_t)t.w * (size_t)t.h;
@@ -206,15 +207,16 @@ size_t rtc_scene_set_packing_(rtc::DevScene& d, const uint32_t res[3])
     return nb;
 }
 
-int rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uint32_t num_materials)
+int rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uint32_t num_materials, const void* const* preset)
 {
     if (!materials || num_materials == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "scene has no materials");
     std::vector<rtc::DevMaterial> mats(num_materials);
     std::vector<std::pair<const float*, void*>> seen;
     for (uint32_t m = 0; m < num_materials; ++m) {
-        if (int rc = upload_texture(s, materials[m].base_color, 3, &mats[m].base, seen)) return rc;
-        if (int rc = upload_texture(s, materials[m].emissive, 3, &mats[m].emissive, seen)) return rc;
-        if (int rc = upload_texture(s, materials[m].transparency, 1, &mats[m].alpha, seen)) return rc;
+        const void* const* pm = preset ? preset + 3 * (size_t)m : nullptr;
+        if (int rc = upload_texture(s, materials[m].base_color, 3, &mats[m].base, seen, pm ? pm[0] : nullptr)) return rc;
+        if (int rc = upload_texture(s, materials[m].emissive, 3, &mats[m].emissive, seen, pm ? pm[1] : nullptr)) return rc;
+        if (int rc = upload_texture(s, materials[m].transparency, 1, &mats[m].alpha, seen, pm ? pm[2] : nullptr)) return rc;
     }
     rtc::DevMaterial* d_mats = nullptr;
     if (int rc = s->alloc(&d_mats, mats.size())) return rc;

@@ -375,6 +375,32 @@ __global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Texel linearisation (stb_image.h:1856-1877 + src/stage1.zig:433-440, 455-468) on the device: the decoded
+// 8-bit RGBA image goes up once (4 B/texel instead of 12-16 B of floats), every texture made from it is one
+// launch. lut = pow(c/255, 2.2) evaluated in double on the host and rounded to float (256 entries); the
+// per-texel arithmetic is one fp32 multiply by the material's factor (RGB), c/255 in fp32 (BLEND) or a compare
+// of that against alphaCutoff (MASK) — bit-identical to the host loader's.
+__global__ void __launch_bounds__(kThreads) k_texels_rgb(const uchar4* __restrict__ img, uint32_t n, const float* __restrict__ lut,
+                                                         float k0, float k1, float k2, float4* __restrict__ out)
+{
+    __shared__ float s_lut[256];
+    s_lut[threadIdx.x] = lut[threadIdx.x];          // kThreads == 256
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) {
+        const uchar4 c = __ldg(img + i);
+        out[i] = make_float4(s_lut[c.x] * k0, s_lut[c.y] * k1, s_lut[c.z] * k2, 0.0f);
+    }
+}
+__global__ void __launch_bounds__(kThreads) k_texels_alpha(const uchar4* __restrict__ img, uint32_t n, uint32_t mask, float cutoff,
+                                                           float* __restrict__ out)
+{
+    for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) {
+        const float a = (float)__ldg(img + i).w / 255.0f;
+        out[i] = mask ? (a > cutoff ? 1.0f : 0.0f) : a;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Host side of the build. Everything is allocated with cudaMalloc and owned by `Built` until released.
 struct Built {
     rtc_grid grid{};
@@ -618,10 +644,60 @@ extern "C" int rtc_geometry_build_device(const float* positions, const rtc_tri_d
     }
 }
 
+// The plan's image-backed textures on the device: every image is uploaded once as RGBA8, every recipe is one
+// launch into `alloc`-ed memory (the scene's, or scratch). preset[3*material + slot] receives the device texels.
+template <typename Alloc>
+static int textures_on_device(const RtcGltfPlan& plan, Alloc&& alloc, std::vector<void*>* scratch, std::vector<const void*>* preset, float* ms)
+{
+    preset->assign(3 * plan.materials.size(), nullptr);
+    if (plan.recipes.empty()) return RTC_OK;
+    float* d_lut = nullptr;
+    if (int rc = rtc::build::dalloc(&d_lut, 256, scratch)) return rc;
+    RTC_CU(cudaMemcpy(d_lut, plan.lut, sizeof plan.lut, cudaMemcpyHostToDevice));
+    std::vector<uchar4*> d_img(plan.images8.size(), nullptr);
+    cudaEvent_t e0, e1;
+    RTC_CU(cudaEventCreate(&e0));
+    RTC_CU(cudaEventCreate(&e1));
+    struct EvGuard { cudaEvent_t a, b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } evg{ e0, e1 };
+    for (const RtcTexelRecipe& r : plan.recipes) {                     // uploads first, so that the kernels run back to back
+        const RtcImage8& im = plan.images8[r.image];
+        const size_t n = (size_t)im.w * im.h;
+        if (n == 0 || n > ((size_t)1 << 30)) return rtc_fail_(RTC_ERR_UNSUPPORTED, "texture image %u is empty or larger than 2^30 texels", r.image);
+        if (!d_img[r.image]) {
+            if (int rc = rtc::build::dalloc(&d_img[r.image], n, scratch)) return rc;
+            RTC_CU(cudaMemcpyAsync(d_img[r.image], im.rgba.data(), n * 4, cudaMemcpyHostToDevice, nullptr));
+        }
+    }
+    std::vector<void*> outs(plan.recipes.size(), nullptr);
+    for (size_t i = 0; i < plan.recipes.size(); ++i) {
+        const RtcTexelRecipe& r = plan.recipes[i];
+        const size_t n = (size_t)plan.images8[r.image].w * plan.images8[r.image].h;
+        if (r.kind == RTC_TEXEL_RGB) { float4* o = nullptr; if (int rc = alloc(&o, n)) return rc; outs[i] = o; }
+        else { float* o = nullptr; if (int rc = alloc(&o, n)) return rc; outs[i] = o; }
+    }
+    RTC_CU(cudaEventRecord(e0, nullptr));
+    for (size_t i = 0; i < plan.recipes.size(); ++i) {
+        const RtcTexelRecipe& r = plan.recipes[i];
+        const uint32_t n = plan.images8[r.image].w * plan.images8[r.image].h;
+        const unsigned blocks = (unsigned)std::min<uint64_t>(((uint64_t)n + kThreads - 1) / kThreads, 148u * 16u);
+        if (r.kind == RTC_TEXEL_RGB)
+            rtc::build::k_texels_rgb<<<blocks, kThreads>>>(d_img[r.image], n, d_lut, r.k[0], r.k[1], r.k[2], (float4*)outs[i]);
+        else
+            rtc::build::k_texels_alpha<<<blocks, kThreads>>>(d_img[r.image], n, r.kind == RTC_TEXEL_ALPHA_MASK ? 1u : 0u, r.k[0], (float*)outs[i]);
+        (*preset)[3 * (size_t)r.material + r.slot] = outs[i];
+    }
+    RTC_CU(cudaEventRecord(e1, nullptr));
+    RTC_CU(cudaEventSynchronize(e1));
+    RTC_CU(cudaGetLastError());
+    if (ms) RTC_CU(cudaEventElapsedTime(ms, e0, e1));
+    return RTC_OK;
+}
+
 // The scene around a soup that is already on the device (b.d_pos / b.d_data): grid build, packed layout, bake,
 // materials. Shared by the soup and the glTF entry points.
 static int scene_from_built(rtc_scene* s, rtc::build::Built& b, uint32_t num_tris, const uint32_t res[3],
-                            const rtc_material* materials, uint32_t num_materials, rtc_build_info* info)
+                            const rtc_material* materials, uint32_t num_materials, rtc_build_info* info,
+                            const void* const* preset = nullptr)
 {
     if (int rc = rtc::build::grid_build(num_tris, res, nullptr, &b)) return rc;
     rtc::DevScene& d = s->dev;
@@ -664,7 +740,7 @@ static int scene_from_built(rtc_scene* s, rtc::build::Built& b, uint32_t num_tri
         info->empty_cells = b.empty_cells; info->min_tris = b.min_tris; info->max_tris = b.max_tris;
         info->device_ms = b.device_ms; info->assemble_ms = b.assemble_ms;
     }
-    if (int rc = rtc_scene_upload_materials_(s, materials, num_materials)) return rc;
+    if (int rc = rtc_scene_upload_materials_(s, materials, num_materials, preset)) return rc;
     return rtc_scene_finish_(s);
 }
 
@@ -722,7 +798,12 @@ extern "C" int rtc_scene_create_from_gltf(const char* path, const char* camera_n
         auto body = [&]() -> int {
             rtc::build::Built b;
             if (int rc = rtc::build::soup_assemble(plan, nullptr, &b)) return rc;
-            return scene_from_built(s, b, plan.num_tris, res, plan.materials.data(), (uint32_t)plan.materials.size(), info);
+            std::vector<const void*> preset;
+            float texel_ms = 0.0f;
+            if (int rc = textures_on_device(plan, [&](auto** p, size_t n) { return s->alloc(p, n); }, &b.tmp, &preset, &texel_ms)) return rc;
+            if (int rc = scene_from_built(s, b, plan.num_tris, res, plan.materials.data(), (uint32_t)plan.materials.size(), info, preset.data())) return rc;
+            if (info) info->assemble_ms += texel_ms;
+            return RTC_OK;
         };
         const int rc = body();
         if (rc != RTC_OK) { rtc_keep_error_free_(s); return rc; }
@@ -753,6 +834,25 @@ extern "C" int rtc_gltf_load_device(const char* path, const char* camera_name, u
         if (plan.num_tris) {
             RTC_CU(cudaMemcpy(own->positions.data(), b.d_pos, own->positions.size() * sizeof(float), cudaMemcpyDeviceToHost));
             RTC_CU(cudaMemcpy(own->tri_data.data(), b.d_data, own->tri_data.size() * sizeof(rtc_tri_data), cudaMemcpyDeviceToHost));
+        }
+        std::vector<const void*> preset;
+        if (int rc = textures_on_device(plan, [&](auto** p, size_t n) { return rtc::build::dalloc(p, n, &b.tmp); }, &b.tmp, &preset, nullptr)) return rc;
+        for (const RtcTexelRecipe& r : plan.recipes) {                  // back to the host in rtc_texture's layout (3 or 1 floats per texel)
+            const size_t n = (size_t)plan.images8[r.image].w * plan.images8[r.image].h;
+            const void* d = preset[3 * (size_t)r.material + r.slot];
+            std::vector<float> px;
+            if (r.kind == RTC_TEXEL_RGB) {
+                std::vector<float4> tmp4(n);
+                RTC_CU(cudaMemcpy(tmp4.data(), d, n * sizeof(float4), cudaMemcpyDeviceToHost));
+                px.resize(3 * n);
+                for (size_t i = 0; i < n; ++i) { px[3 * i] = tmp4[i].x; px[3 * i + 1] = tmp4[i].y; px[3 * i + 2] = tmp4[i].z; }
+            } else {
+                px.resize(n);
+                RTC_CU(cudaMemcpy(px.data(), d, n * sizeof(float), cudaMemcpyDeviceToHost));
+            }
+            plan.texels.push_back(std::move(px));
+            rtc_material& m = plan.materials[r.material];
+            (r.slot == 0 ? m.base_color : (r.slot == 1 ? m.emissive : m.transparency)).texels = plan.texels.back().data();
         }
         own->materials = std::move(plan.materials);
         own->texels = std::move(plan.texels);

@@ -148,6 +148,7 @@ struct Image {
     uint32_t w = 0, h = 0;
     int actual_c = 0;
     std::vector<float> data;           // w*h*4 linear floats, what stbi_loadf_from_memory(..., 4) returns
+    std::vector<uint8_t> rgba8;        // deferred mode: the decoded 8-bit image, linearised on the device instead
 };
 
 struct Asset {
@@ -155,6 +156,7 @@ struct Asset {
     std::string dir;
     std::vector<std::vector<uint8_t>> buffers;
     std::vector<Image> images;
+    bool defer_texels = false;         // images stay 8-bit, textures become recipes (rtc_gltf_plan.h)
     std::vector<int> parent;           // per node, -1 = root (zgltf main.zig:1246-1295)
 };
 
@@ -186,12 +188,16 @@ void fill_parents(const Json& nodes, std::vector<int>& parent, size_t node, int 
 
 // stb_image.h:1856-1877 (stbi__ldr_to_hdr): colour channels pow(c/255, 2.2) * 1.0 evaluated in double and
 // rounded to float; the alpha channel is c/255 in float.
+void linear_lut(float lut[256])
+{
+    for (int i = 0; i < 256; ++i) lut[i] = (float)(pow((double)((float)i / 255.0f), 2.2) * 1.0);
+}
 void linearise(const rtc_host::DecodedImage& src, Image& dst)
 {
     static float lut[256];
     static std::atomic<bool> ready{ false };
     if (!ready.load()) {
-        for (int i = 0; i < 256; ++i) lut[i] = (float)(pow((double)((float)i / 255.0f), 2.2) * 1.0);
+        linear_lut(lut);
         ready.store(true);
     }
     dst.w = src.w; dst.h = src.h; dst.actual_c = src.actual_c;
@@ -278,7 +284,12 @@ void load_asset(const std::string& path, int threads, Asset& a)
                     if (bytes.n >= 3 && bytes.p[0] == 0xFF && bytes.p[1] == 0xD8)
                         fail(RTC_ERR_UNSUPPORTED, "glTF: image " + std::to_string(i) + " is a JPEG; this host decodes PNG textures only");
                     try {
-                        linearise(rtc_host::png_decode(bytes.p, bytes.n), a.images[i]);
+                        if (a.defer_texels) {
+                            rtc_host::DecodedImage dec = rtc_host::png_decode(bytes.p, bytes.n);
+                            Image& im8 = a.images[i];
+                            im8.w = dec.w; im8.h = dec.h; im8.actual_c = dec.actual_c; im8.rgba8 = std::move(dec.rgba);
+                        } else
+                            linearise(rtc_host::png_decode(bytes.p, bytes.n), a.images[i]);
                     } catch (const std::runtime_error& e) {
                         fail(RTC_ERR_UNSUPPORTED, "glTF: image " + std::to_string(i) + ": " + e.what());
                     }
@@ -543,11 +554,25 @@ const Image& image_of(const Asset& a, const Json& texture)
     return a.images[(size_t)src];
 }
 // loadColorTexture (src/stage1.zig:427-446): rgb of the image times the factor, or a 1x1 texture of the factor.
-rtc_texture color_texture(const Asset& a, HostScene& out, const Json* info, const float factor[3])
+// Deferred mode: the texture's texels are left null and a recipe (image, kind, constants) is recorded instead.
+struct Recipes {
+    std::vector<RtcTexelRecipe>* list = nullptr;
+    uint32_t material = 0, slot = 0;
+    void add(const Asset& a, const Image& im, uint32_t kind, const float k[3]) const
+    {
+        RtcTexelRecipe r;
+        r.material = material; r.slot = slot; r.image = (uint32_t)(&im - a.images.data()); r.kind = kind;
+        r.k[0] = k[0]; r.k[1] = k[1]; r.k[2] = k[2];
+        list->push_back(r);
+    }
+};
+
+rtc_texture color_texture(const Asset& a, HostScene& out, const Json* info, const float factor[3], const Recipes& rec)
 {
     if (!info) return dummy_texture(out, factor, 3);
     const Json& texture = item(a.doc, "textures", info->integer("index", -1));
     const Image& im = image_of(a, texture);
+    if (rec.list) { rec.add(a, im, RTC_TEXEL_RGB, factor); return make_texture(a, texture, im, nullptr, 3); }
     const size_t n = (size_t)im.w * im.h;
     std::vector<float> px(n * 3);
     for (size_t i = 0; i < n; ++i)
@@ -556,7 +581,7 @@ rtc_texture color_texture(const Asset& a, HostScene& out, const Json* info, cons
     return make_texture(a, texture, im, out.texels.back().data(), 3);
 }
 // loadTransparencyTexture (src/stage1.zig:448-472).
-rtc_texture transparency_texture(const Asset& a, HostScene& out, const Json& material)
+rtc_texture transparency_texture(const Asset& a, HostScene& out, const Json& material, const Recipes& rec)
 {
     const float one = 1.0f;
     const std::string mode = material.string("alphaMode", "OPAQUE");
@@ -567,6 +592,11 @@ rtc_texture transparency_texture(const Asset& a, HostScene& out, const Json& mat
         const Image& im = image_of(a, texture);
         if (im.actual_c == 4 || im.actual_c == 2) {
             const float cutoff = (float)material.number("alphaCutoff", 0.5);
+            if (rec.list) {
+                const float k[3] = { cutoff, 0.0f, 0.0f };
+                rec.add(a, im, mode == "MASK" ? RTC_TEXEL_ALPHA_MASK : RTC_TEXEL_ALPHA, k);
+                return make_texture(a, texture, im, nullptr, 1);
+            }
             const size_t n = (size_t)im.w * im.h;
             std::vector<float> px(n);
             for (size_t i = 0; i < n; ++i) {
@@ -580,9 +610,12 @@ rtc_texture transparency_texture(const Asset& a, HostScene& out, const Json& mat
     return dummy_texture(out, &one, 1);
 }
 // loadMaterials (src/stage1.zig:474-496). metallic/roughness, normal maps, emissive_strength: ignored there too.
-void load_materials(const Asset& a, HostScene& out)
+void load_materials(const Asset& a, HostScene& out, std::vector<RtcTexelRecipe>* recipes = nullptr)
 {
+    Recipes rec;
+    rec.list = recipes;
     for (const Json& m : arr_of(a.doc, "materials").arr) {
+        rec.material = (uint32_t)out.materials.size();
         float base[3] = { 1.0f, 1.0f, 1.0f }, emis[3] = { 0.0f, 0.0f, 0.0f };
         const Json* pbr = m.find("pbrMetallicRoughness");
         if (pbr)
@@ -591,9 +624,9 @@ void load_materials(const Asset& a, HostScene& out)
         if (const Json* f = m.find("emissiveFactor"))
             for (size_t i = 0; i < 3 && i < f->arr.size(); ++i) emis[i] = (float)f->arr[i].num;
         rtc_material mat;
-        mat.base_color = color_texture(a, out, pbr ? pbr->find("baseColorTexture") : nullptr, base);
-        mat.emissive = color_texture(a, out, m.find("emissiveTexture"), emis);
-        mat.transparency = transparency_texture(a, out, m);
+        rec.slot = 0; mat.base_color = color_texture(a, out, pbr ? pbr->find("baseColorTexture") : nullptr, base, rec);
+        rec.slot = 1; mat.emissive = color_texture(a, out, m.find("emissiveTexture"), emis, rec);
+        rec.slot = 2; mat.transparency = transparency_texture(a, out, m, rec);
         out.materials.push_back(mat);
     }
 }
@@ -621,11 +654,18 @@ int rtc_gltf_plan_(const char* path, const char* camera_name, uint32_t width, ui
 {
     return guarded([&] {
         Asset a;
+        a.defer_texels = true;
         load_asset(path, num_threads, a);
         HostScene hs;
         load_camera(a, camera_name, width, height, &out->camera);     // order of src/main.zig:109-112
-        load_materials(a, hs);
+        load_materials(a, hs, &out->recipes);
         plan_geometry(a, *out);
+        linear_lut(out->lut);
+        out->images8.resize(a.images.size());
+        for (size_t i = 0; i < a.images.size(); ++i) {
+            out->images8[i].w = a.images[i].w; out->images8[i].h = a.images[i].h;
+            out->images8[i].rgba = std::move(a.images[i].rgba8);
+        }
         out->materials = std::move(hs.materials);
         out->texels = std::move(hs.texels);          // moving the outer vector keeps the inner data() pointers
         out->num_images = (uint32_t)a.images.size();

@@ -30,6 +30,22 @@ struct RtcHostSceneOwner {
     std::vector<std::vector<float>> texels;      // owners of rtc_texture.texels
 };
 
+// A texture whose texels are produced on the device from a decoded 8-bit image (rtc_build.cu: k_texels):
+//   RGB         rgb = lut[c] * k   (stb's pow(c/255, 2.2) table, times the material's factor; stage1.zig:427-446)
+//   ALPHA       a = c/255          (alphaMode BLEND; stage1.zig:448-472)
+//   ALPHA_MASK  a > k[0] ? 1 : 0   (alphaMode MASK, k[0] = alphaCutoff)
+// The rtc_material's texture has texels == nullptr; w, h, channels and the clamp range are set.
+enum { RTC_TEXEL_RGB = 0, RTC_TEXEL_ALPHA = 1, RTC_TEXEL_ALPHA_MASK = 2 };
+struct RtcTexelRecipe {
+    uint32_t material, slot;       // slot: 0 base colour, 1 emissive, 2 transparency
+    uint32_t image, kind;
+    float k[3];
+};
+struct RtcImage8 {
+    uint32_t w = 0, h = 0;
+    std::vector<uint8_t> rgba;     // w*h*4
+};
+
 struct RtcGltfPlan {
     rtc_camera camera{};
     std::vector<std::vector<uint8_t>> buffers;     // the asset's buffers (moved out of the loader)
@@ -38,7 +54,10 @@ struct RtcGltfPlan {
     std::vector<RtcPrimRef> prims;                 // num_tris > 0 only
     uint32_t num_tris = 0;
     std::vector<rtc_material> materials;
-    std::vector<std::vector<float>> texels;        // owners of materials[].*.texels
+    std::vector<std::vector<float>> texels;        // owners of materials[].*.texels (1x1 constants)
+    std::vector<RtcTexelRecipe> recipes;           // the textures that come from images
+    std::vector<RtcImage8> images8;
+    float lut[256];                                // stb's ldr -> linear table (computed in double on the host)
     uint32_t num_images = 0;
 };
 

@@ -73,7 +73,9 @@ struct rtc_scene {
 int  rtc_scene_new_(int device, rtc_scene** out);                  // device checks + empty scene object
 void rtc_scene_free_(rtc_scene* s);
 void rtc_keep_error_free_(rtc_scene* s);                            // frees the scene, keeps rtc_last_error()
-int  rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uint32_t num_materials);
+// preset: NULL, or 3 entries per material (base colour, emissive, transparency): non-null = that texture's texels are
+// already on the device in the device layout (float4 rgb0 / float) and are used as they are.
+int  rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uint32_t num_materials, const void* const* preset = nullptr);
 int  rtc_scene_finish_(rtc_scene* s);                              // counters, stream, events
 // packed-cell geometry of a grid resolution (rtc_device.cuh): fills dev.mask/shift, returns the padded block count
 size_t rtc_scene_set_packing_(rtc::DevScene& d, const uint32_t res[3]);
