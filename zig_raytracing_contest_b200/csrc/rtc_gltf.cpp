@@ -12,7 +12,13 @@
 #include "rtc_json.h"
 #include "rtc_png.h"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -35,8 +41,25 @@ struct HostError {
 };
 [[noreturn]] void fail(int code, const std::string& msg) { throw HostError{ code, msg }; }
 
-std::vector<uint8_t> read_file(const std::string& path)
+// The file as a read-only mapping (the 100 MB-class .bin / .glb files the loader exists for); anything that
+// cannot be mapped (pipes, empty files) is read.
+RtcBytes read_file(const std::string& path)
 {
+    const int fd = open(path.c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd < 0) fail(RTC_ERR_IO, "cannot open '" + path + "'");
+    struct stat st;
+    if (fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0) {
+        const size_t n = (size_t)st.st_size;
+        void* m = mmap(nullptr, n, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+        if (m != MAP_FAILED) {
+            close(fd);
+            RtcBytes r;
+            r.map = std::shared_ptr<const void>(m, [n](const void* q) { munmap(const_cast<void*>(q), n); });
+            r.p = static_cast<const uint8_t*>(m); r.n = n;
+            return r;
+        }
+    }
+    close(fd);
     std::ifstream f(path, std::ios::binary);
     if (!f) fail(RTC_ERR_IO, "cannot open '" + path + "'");
     f.seekg(0, std::ios::end);
@@ -44,7 +67,7 @@ std::vector<uint8_t> read_file(const std::string& path)
     f.seekg(0, std::ios::beg);
     std::vector<uint8_t> data((size_t)n);
     if (n && !f.read((char*)data.data(), n)) fail(RTC_ERR_IO, "cannot read '" + path + "'");
-    return data;
+    return RtcBytes(std::move(data));
 }
 
 std::string dir_of(const std::string& path)
@@ -75,12 +98,12 @@ std::vector<uint8_t> base64_decode(const std::string& s, size_t from)
 }
 
 // A uri of a buffer or image: a data: URI (base64) or a path relative to the asset (src/stage1.zig:47,92).
-std::vector<uint8_t> load_uri(const std::string& dir, const std::string& uri)
+RtcBytes load_uri(const std::string& dir, const std::string& uri)
 {
     if (uri.compare(0, 5, "data:") == 0) {
         const size_t k = uri.find("base64,");
         if (k == std::string::npos) fail(RTC_ERR_FORMAT, "data: URI without base64 payload");
-        return base64_decode(uri, k + 7);
+        return RtcBytes(base64_decode(uri, k + 7));
     }
     std::string rel;
     for (size_t i = 0; i < uri.size(); ++i) {             // percent-decoding of the relative path
@@ -154,7 +177,7 @@ struct Image {
 struct Asset {
     Json doc;
     std::string dir;
-    std::vector<std::vector<uint8_t>> buffers;
+    std::vector<RtcBytes> buffers;
     std::vector<Image> images;
     bool defer_texels = false;         // images stay 8-bit, textures become recipes (rtc_gltf_plan.h)
     std::vector<int> parent;           // per node, -1 = root (zgltf main.zig:1246-1295)
@@ -224,23 +247,23 @@ BufferSpan view_bytes(const Asset& a, long long view_idx)
 // (image i is decoded by thread i % threads, src/stage1.zig:36-37).
 void load_asset(const std::string& path, int threads, Asset& a)
 {
-    std::vector<uint8_t> file = read_file(path);
+    RtcBytes file = read_file(path);
     a.dir = dir_of(path);
-    std::vector<uint8_t> glb_bin;
+    RtcBytes glb_bin;
     bool has_glb_bin = false;
     if (file.size() >= 12 && memcmp(file.data(), "glTF", 4) == 0) {                     // GLB container
         size_t p = 12;
-        std::vector<uint8_t> json;
+        RtcBytes json;
         while (p + 8 <= file.size()) {
             uint32_t len, type;
             memcpy(&len, file.data() + p, 4); memcpy(&type, file.data() + p + 4, 4);
             if (p + 8 + (size_t)len > file.size()) fail(RTC_ERR_FORMAT, "GLB: truncated chunk");
-            if (type == 0x4E4F534Au) json.assign(file.begin() + p + 8, file.begin() + p + 8 + len);
-            else if (type == 0x004E4942u && !has_glb_bin) { glb_bin.assign(file.begin() + p + 8, file.begin() + p + 8 + len); has_glb_bin = true; }
+            if (type == 0x4E4F534Au) json = file.window(p + 8, len);
+            else if (type == 0x004E4942u && !has_glb_bin) { glb_bin = file.window(p + 8, len); has_glb_bin = true; }
             p += 8 + (size_t)len;
         }
         if (json.empty()) fail(RTC_ERR_FORMAT, "GLB: no JSON chunk");
-        file.swap(json);
+        file = std::move(json);
     }
     try {
         a.doc = rtc_host::JsonParser((const char*)file.data(), file.size()).parse();
@@ -276,7 +299,7 @@ void load_asset(const std::string& path, int threads, Asset& a)
             try {
                 for (size_t i = (size_t)t; i < imgs.arr.size(); i += (size_t)T) {
                     const Json& im = imgs.arr[i];
-                    std::vector<uint8_t> owned;
+                    RtcBytes owned;
                     BufferSpan bytes{ nullptr, 0 };
                     if (im.has("bufferView")) bytes = view_bytes(a, im.integer("bufferView", -1));
                     else if (im.has("uri")) { owned = load_uri(a.dir, im.string("uri", "")); bytes = BufferSpan{ owned.data(), owned.size() }; }
@@ -408,28 +431,59 @@ void for_each_primitive(const Asset& a, F&& f)
     }
 }
 
-void load_geometry(const Asset& a, HostScene& out)
+// The reference fills the soup serially on its main thread; here the primitives are collected first and the
+// triangles are filled by `threads` workers over equal slices of the soup (same values, same order).
+void load_geometry(const Asset& a, HostScene& out, int threads)
 {
+    struct Prim { Mat4 matrix; uint32_t material; Accessor pos, nrm, uv, ind; bool has_uv; size_t first, tris; };
+    std::vector<Prim> prims;
+    size_t total = 0;
     for_each_primitive(a, [&](const Mat4& matrix, uint32_t material, const Accessor& pos, const Accessor& nrm,
                               const Accessor& uv, bool has_uv, const Accessor& ind) {
         const size_t tris = ind.count / 3;
-        for (size_t t = 0; t < tris; ++t) {
+        if (!tris) return;
+        prims.push_back(Prim{ matrix, material, pos, nrm, uv, ind, has_uv, total, tris });
+        total += tris;
+    });
+    if (total > 0xFFFFFFFFull) fail(RTC_ERR_UNSUPPORTED, "glTF: more than 2^32 - 1 triangles");
+    const auto tr0 = std::chrono::steady_clock::now();
+    out.positions.resize(total * 9);
+    out.tri_data.resize(total);
+    if (getenv("RTC_TRACE_LOAD")) fprintf(stderr, "  resize %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tr0).count());
+    std::atomic<bool> bad{ false };
+    auto fill = [&](size_t g0, size_t g1) {
+        size_t k = 0;
+        while (k + 1 < prims.size() && prims[k + 1].first <= g0) ++k;
+        for (size_t g = g0; g < g1; ++g) {
+            while (g >= prims[k].first + prims[k].tris) ++k;
+            const Prim& pr = prims[k];
+            const size_t t = g - pr.first;
             rtc_tri_data d;
             memset(&d, 0, sizeof d);
-            d.material = material;
-            d.src_tri = (uint32_t)out.tri_data.size();
+            d.material = pr.material;
+            d.src_tri = (uint32_t)g;
             for (int i = 0; i < 3; ++i) {
-                const uint32_t v = read_index(ind, t * 3 + (size_t)i);
-                if (v >= pos.count || v >= nrm.count || (has_uv && v >= uv.count)) fail(RTC_ERR_FORMAT, "glTF: vertex index out of range");
-                const V3 p = transform_position(matrix, read_v3(pos, v));
-                const V3 nn = normalize(transform_direction(matrix, read_v3(nrm, v)));     // not the inverse transpose (TODO in the reference)
-                out.positions.push_back(p.x); out.positions.push_back(p.y); out.positions.push_back(p.z);
+                const uint32_t v = read_index(pr.ind, t * 3 + (size_t)i);
+                if (v >= pr.pos.count || v >= pr.nrm.count || (pr.has_uv && v >= pr.uv.count)) { bad.store(true); return; }
+                const V3 p = transform_position(pr.matrix, read_v3(pr.pos, v));
+                const V3 nn = normalize(transform_direction(pr.matrix, read_v3(pr.nrm, v)));     // not the inverse transpose (TODO in the reference)
+                float* po = out.positions.data() + 9 * g + 3 * (size_t)i;
+                po[0] = p.x; po[1] = p.y; po[2] = p.z;
                 d.normal[i][0] = nn.x; d.normal[i][1] = nn.y; d.normal[i][2] = nn.z;
-                if (has_uv) memcpy(d.texcoord[i], uv.base + v * uv.stride, 8);
+                if (pr.has_uv) memcpy(d.texcoord[i], pr.uv.base + v * pr.uv.stride, 8);
             }
-            out.tri_data.push_back(d);
+            out.tri_data[g] = d;
         }
-    });
+    };
+    const size_t T = (size_t)(threads < 1 ? 1 : threads);
+    const size_t workers = total < 65536 ? 1 : T;
+    if (workers == 1) { if (total) fill(0, total); }
+    else {
+        std::vector<std::thread> pool;
+        for (size_t w = 0; w < workers; ++w) pool.emplace_back(fill, total * w / workers, total * (w + 1) / workers);
+        for (auto& th : pool) th.join();
+    }
+    if (bad.load()) fail(RTC_ERR_FORMAT, "glTF: vertex index out of range");
 }
 
 // The same walk with the per-triangle loop left to the device (rtc_build.cu: k_assemble): one table row per
@@ -681,12 +735,20 @@ int rtc_gltf_load(const char* path, const char* camera_name, uint32_t width, uin
     if (!path || !out) return rtc_set_error_(RTC_ERR_INVALID_ARGUMENT, "rtc_gltf_load: null argument");
     memset(out, 0, sizeof *out);
     return guarded([&] {
+        const bool trace = getenv("RTC_TRACE_LOAD") != nullptr;
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        const auto t0 = now();
         Asset a;
         load_asset(path, num_threads, a);
+        const auto t1 = now();
         std::unique_ptr<HostScene> hs(new HostScene());
         load_camera(a, camera_name, width, height, &out->camera);     // order of src/main.zig:109-112
         load_materials(a, *hs);
-        load_geometry(a, *hs);
+        const auto t2 = now();
+        load_geometry(a, *hs, num_threads);
+        const auto t3 = now();
+        if (trace) fprintf(stderr, "rtc_gltf_load: files+images %.1f ms, camera+materials %.1f ms, triangles %.1f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, t3));
         out->positions = hs->positions.data();
         out->tri_data = hs->tri_data.data();
         out->num_tris = (uint32_t)hs->tri_data.size();
@@ -710,7 +772,7 @@ int rtc_config_load(const char* path, rtc_config* out)
 {
     if (!path || !out) return rtc_set_error_(RTC_ERR_INVALID_ARGUMENT, "rtc_config_load: null argument");
     return guarded([&] {
-        const std::vector<uint8_t> file = read_file(path);
+        const RtcBytes file = read_file(path);
         const Json doc = rtc_host::JsonParser((const char*)file.data(), file.size()).parse();
         if (doc.kind != Json::Object) fail(RTC_ERR_FORMAT, "config.json: not an object");
         for (const auto& kv : doc.obj)
@@ -748,7 +810,7 @@ int rtc_png_read(const char* path, uint32_t* w, uint32_t* h, uint8_t** rgb_out)
 {
     if (!path || !w || !h || !rgb_out) return rtc_set_error_(RTC_ERR_INVALID_ARGUMENT, "rtc_png_read: null argument");
     return guarded([&] {
-        const std::vector<uint8_t> file = read_file(path);
+        const RtcBytes file = read_file(path);
         rtc_host::DecodedImage img;
         try { img = rtc_host::png_decode(file.data(), file.size()); }
         catch (const std::runtime_error& e) { fail(RTC_ERR_FORMAT, e.what()); }

@@ -4,8 +4,33 @@
 #pragma once
 #include "../../include/rtc.h"
 
+#include <cstddef>
 #include <cstdint>
+#include <memory>
+#include <new>
+#include <utility>
 #include <vector>
+
+// Bytes of a file or a glTF buffer: owned (base64 payloads) or a window into a read-only mapping of the file
+// (no read() into a zero-filled vector, no copy of a .glb's binary chunk). Reads like a vector.
+struct RtcBytes {
+    std::vector<uint8_t> own;
+    std::shared_ptr<const void> map;       // keeps the mapping alive; null = `own` holds the bytes
+    const uint8_t* p = nullptr;
+    size_t n = 0;
+    RtcBytes() = default;
+    RtcBytes(std::vector<uint8_t>&& v) : own(std::move(v)) {}
+    const uint8_t* data() const { return map ? p : own.data(); }
+    size_t size() const { return map ? n : own.size(); }
+    bool empty() const { return size() == 0; }
+    RtcBytes window(size_t off, size_t len) const       // of a mapping: shares it; of owned bytes: a copy
+    {
+        RtcBytes r;
+        if (map) { r.map = map; r.p = p + off; r.n = len; }
+        else r.own.assign(own.begin() + (ptrdiff_t)off, own.begin() + (ptrdiff_t)(off + len));
+        return r;
+    }
+};
 
 // One mesh primitive of one node, in the reference's visiting order (nodes in file order, primitives in mesh
 // order). Offsets are bytes from the start of the device blob the buffers are uploaded into (RtcGltfPlan::
@@ -22,10 +47,19 @@ struct RtcPrimRef {
     uint32_t first_tri, num_tris;  // position in the soup
 };
 
+// vector::resize without the zero fill: the soup arrays are hundreds of MB that are overwritten right away, and the
+// first touch of their pages then happens in the worker threads that fill them.
+template <class T>
+struct RtcNoInit : std::allocator<T> {
+    template <class U> struct rebind { using other = RtcNoInit<U>; };
+    template <class U> void construct(U* p) { ::new ((void*)p) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+
 // What an rtc_host_scene's `owner` points at (rtc_host_scene_free deletes it).
 struct RtcHostSceneOwner {
-    std::vector<float> positions;
-    std::vector<rtc_tri_data> tri_data;
+    std::vector<float, RtcNoInit<float>> positions;
+    std::vector<rtc_tri_data, RtcNoInit<rtc_tri_data>> tri_data;
     std::vector<rtc_material> materials;
     std::vector<std::vector<float>> texels;      // owners of rtc_texture.texels
 };
@@ -48,7 +82,7 @@ struct RtcImage8 {
 
 struct RtcGltfPlan {
     rtc_camera camera{};
-    std::vector<std::vector<uint8_t>> buffers;     // the asset's buffers (moved out of the loader)
+    std::vector<RtcBytes> buffers;                 // the asset's buffers (moved out of the loader)
     std::vector<uint64_t> buffer_base;             // per buffer: offset in the device blob, or ~0 = not referenced
     uint64_t blob_bytes = 0;
     std::vector<RtcPrimRef> prims;                 // num_tris > 0 only
