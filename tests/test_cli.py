@@ -161,6 +161,35 @@ def test_png_roundtrip_and_decoder_colour_types(tmp_path):
     assert np.array_equal(rtc.png_read(str(tmp_path / "q.png")), rgba[:, :, :3])
 
 
+def test_png_encoder_slices_are_one_valid_stream(tmp_path, monkeypatch):
+    """A frame larger than several 1 MiB deflate slices: the file decodes with an independent inflater (Python's
+    zlib: one stream, Adler-32 trailer checked) to the same pixels, and its bytes do not depend on the thread count."""
+    import struct
+    import zlib
+    rng = np.random.RandomState(4)
+    h, w = 900, 1400                                       # 3.8 MB of rows -> 4 slices
+    rgb = (np.linspace(0, 255, w)[None, :, None] * np.ones((h, 1, 3))).astype(np.uint8)
+    rgb[::3] = rng.randint(0, 256, (len(rgb[::3]), w, 3)).astype(np.uint8)      # noisy rows next to flat ones
+    files = []
+    for threads in ("1", "3", "16"):
+        monkeypatch.setenv("RTC_PNG_THREADS", threads)
+        path = str(tmp_path / ("t%s.png" % threads))
+        rtc.png_write(path, rgb)
+        files.append(open(path, "rb").read())
+        assert np.array_equal(rtc.png_read(path), rgb)
+    assert files[0] == files[1] == files[2]
+    data, p, idat = files[0], 8, b""
+    while p < len(data):
+        n, typ = struct.unpack(">I4s", data[p:p + 8])
+        body = data[p + 8:p + 8 + n]
+        assert struct.unpack(">I", data[p + 8 + n:p + 12 + n])[0] == zlib.crc32(typ + body)
+        if typ == b"IDAT":
+            idat += body
+        p += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    assert np.all(raw[:, 0] == 0) and np.array_equal(raw[:, 1:].reshape(h, w, 3), rgb)
+
+
 def _run_cli(cwd, *args, env=None):
     return subprocess.run([CLI] + list(args), cwd=str(cwd), capture_output=True, text=True, timeout=300,
                           env=dict(os.environ, **env) if env else None)

@@ -798,7 +798,9 @@ int rtc_png_write(const char* path, uint32_t w, uint32_t h, const uint8_t* rgb)
 {
     if (!path || !rgb || w == 0 || h == 0) return rtc_set_error_(RTC_ERR_INVALID_ARGUMENT, "rtc_png_write: bad argument");
     return guarded([&] {
-        const std::vector<uint8_t> png = rtc_host::png_encode_rgb8(w, h, rgb);
+        int threads = (int)std::thread::hardware_concurrency();
+        if (const char* e = getenv("RTC_PNG_THREADS")) threads = atoi(e);
+        const std::vector<uint8_t> png = rtc_host::png_encode_rgb8(w, h, rgb, threads);
         FILE* f = fopen(path, "wb");
         if (!f) fail(RTC_ERR_IO, std::string("WritePngFail: cannot open '") + path + "'");
         const size_t n = fwrite(png.data(), 1, png.size(), f);

@@ -1,17 +1,20 @@
 // rtc_png.h — PNG in and out for the host side, over zlib.
 //   png_encode_rgb8 : what the reference asks of stb at src/main.zig:130-135 — stbi_write_png(path, w, h, 3,
-//                     img, 3*w): an 8-bit RGB, non-interlaced PNG (pixels identical; the deflate stream is zlib's).
+//                     img, 3*w): an 8-bit RGB, non-interlaced PNG (pixels identical; the deflate stream is zlib's,
+//                     produced in 1 MiB slices on all host threads).
 //   png_decode      : what stage1 asks of stb at src/stage1.zig:56-63 (stbi_loadf_from_memory(..., 4)), for
 //                     PNG inputs: 8-bit RGBA out + the file's own channel count (`actual_c`). 16-bit samples keep
 //                     their high byte (stb's 16 -> 8 conversion); palette + tRNS expand; Adam7 is not supported.
 #pragma once
 #include <zlib.h>
 
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace rtc_host {
@@ -28,7 +31,56 @@ inline void png_chunk(std::vector<uint8_t>& out, const char type[4], const uint8
     be32(out, (uint32_t)crc32(0L, out.data() + at, (uInt)(n + 4)));
 }
 
-inline std::vector<uint8_t> png_encode_rgb8(uint32_t w, uint32_t h, const uint8_t* rgb)
+// The zlib stream of `raw`, deflated in independent slices of kPngSlice bytes on up to `threads` threads: every slice
+// but the last ends in a sync flush (byte-aligned, BFINAL = 0), so the concatenation is one valid deflate stream
+// (the pigz construction, without dictionary priming); the Adler-32 trailer is combined from the slices'. The
+// slice size is fixed, so the bytes do not depend on the thread count. stb's encoder (stb_image_write.h:1128-1229)
+// is a single-threaded deflate of the whole frame — seconds at 4K; the pixels a decoder gets back are the same.
+static constexpr size_t kPngSlice = (size_t)1 << 20;
+inline std::vector<uint8_t> zlib_parallel(const uint8_t* raw, size_t n, int threads)
+{
+    const size_t slices = n ? (n + kPngSlice - 1) / kPngSlice : 1;
+    std::vector<std::vector<uint8_t>> parts(slices);
+    std::vector<uLong> adler(slices, 1);
+    std::atomic<size_t> next{ 0 };
+    std::atomic<bool> failed{ false };
+    auto work = [&] {
+        for (size_t i = next.fetch_add(1); i < slices; i = next.fetch_add(1)) {
+            const size_t off = i * kPngSlice, len = n - off < kPngSlice ? n - off : kPngSlice;
+            z_stream zs;
+            memset(&zs, 0, sizeof zs);
+            if (deflateInit2(&zs, 6, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY) != Z_OK) { failed.store(true); return; }
+            std::vector<uint8_t>& out = parts[i];
+            out.resize(deflateBound(&zs, (uLong)len) + 16);
+            zs.next_in = const_cast<Bytef*>(raw + off); zs.avail_in = (uInt)len;
+            zs.next_out = out.data(); zs.avail_out = (uInt)out.size();
+            const int rc = deflate(&zs, i + 1 == slices ? Z_FINISH : Z_SYNC_FLUSH);
+            if ((i + 1 == slices && rc != Z_STREAM_END) || (i + 1 != slices && (rc != Z_OK || zs.avail_in != 0 || zs.avail_out == 0))) failed.store(true);
+            out.resize(out.size() - zs.avail_out);
+            deflateEnd(&zs);
+            adler[i] = adler32(1L, raw + off, (uInt)len);
+        }
+    };
+    const size_t T = (size_t)(threads < 1 ? 1 : threads) < slices ? (size_t)(threads < 1 ? 1 : threads) : slices;
+    if (T <= 1) work();
+    else {
+        std::vector<std::thread> pool;
+        for (size_t t = 0; t < T; ++t) pool.emplace_back(work);
+        for (auto& th : pool) th.join();
+    }
+    if (failed.load()) throw std::runtime_error("PNG: deflate failed");
+    std::vector<uint8_t> z = { 0x78, 0x9C };
+    uLong a = 1;
+    for (size_t i = 0; i < slices; ++i) {
+        z.insert(z.end(), parts[i].begin(), parts[i].end());
+        const size_t off = i * kPngSlice, len = n - off < kPngSlice ? n - off : kPngSlice;
+        a = i == 0 ? adler[0] : adler32_combine(a, adler[i], (z_off_t)len);
+    }
+    be32(z, (uint32_t)a);
+    return z;
+}
+
+inline std::vector<uint8_t> png_encode_rgb8(uint32_t w, uint32_t h, const uint8_t* rgb, int threads = 1)
 {
     std::vector<uint8_t> raw((size_t)h * (3 * (size_t)w + 1));
     for (uint32_t y = 0; y < h; ++y) {
@@ -36,15 +88,13 @@ inline std::vector<uint8_t> png_encode_rgb8(uint32_t w, uint32_t h, const uint8_
         row[0] = 0;                                               // filter type None
         memcpy(row + 1, rgb + (size_t)y * 3 * w, 3 * (size_t)w);
     }
-    uLongf zn = compressBound((uLong)raw.size());
-    std::vector<uint8_t> z(zn);
-    if (compress2(z.data(), &zn, raw.data(), (uLong)raw.size(), 6) != Z_OK) throw std::runtime_error("PNG: deflate failed");
+    const std::vector<uint8_t> z = zlib_parallel(raw.data(), raw.size(), threads);
     std::vector<uint8_t> out = { 0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n' };
     std::vector<uint8_t> ihdr;
     be32(ihdr, w); be32(ihdr, h);
     ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);
     png_chunk(out, "IHDR", ihdr.data(), ihdr.size());
-    png_chunk(out, "IDAT", z.data(), zn);
+    png_chunk(out, "IDAT", z.data(), z.size());
     png_chunk(out, "IEND", nullptr, 0);
     return out;
 }
