@@ -15,6 +15,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv --log-fil
 # second frame of the run (warm-up step 2), first batch: its four k_trace launches (bounce 0..3)
 ncu --set full --clock-control none --import-source on -k regex:k_trace -s 24 -c 4 -o $out/${tag}_ktrace \
     python bench.py --steps 1 --no-cpu > $out/${tag}_ncu_full.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_bin -c 4 -o $out/${tag}_kbin \
-    python bench.py --workload cfg4_terrain5M_4k_256spp --spp 1 --steps 1 --no-cpu > $out/${tag}_ncu_kbin.log 2>&1
+python tools/stage1_bench.py --tris 2000000 --out $out/${tag}_stage1.json > $out/${tag}_stage1.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"k_assemble|k_texels" -c 6 -o $out/${tag}_kassemble \
+    python tools/stage1_bench.py --tris 2000000 --reps 1 > $out/${tag}_ncu_kassemble.log 2>&1
+python tools/png_bench.py --out $out/${tag}_png.json > /dev/null 2>&1
 echo done
