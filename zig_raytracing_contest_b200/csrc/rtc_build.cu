@@ -329,8 +329,10 @@ __global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict
                                                        uint32_t num_tris, float* __restrict__ pos_out, uint32_t* __restrict__ data_out,
                                                        uint32_t* __restrict__ flag)
 {
-    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;
-    if (g >= num_tris) return;
+    __shared__ __align__(16) float sh_pos[9 * kThreads];
+    __shared__ __align__(16) uint32_t sh_data[17 * kThreads];
+    const uint32_t g0 = blockIdx.x * kThreads;
+    const uint32_t g = min(g0 + threadIdx.x, num_tris - 1u);      // threads past the end redo the last triangle (not stored)
     uint32_t lo = 0u, hi = num_prims;                       // last primitive with first_tri <= g
     while (hi - lo > 1u) {
         const uint32_t mid = (lo + hi) >> 1;
@@ -349,8 +351,10 @@ __global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict
     const uint8_t* b_nrm = blob + __ldg(&pr.off_nrm);
     const uint8_t* b_uv = blob + __ldg(&pr.off_uv);
     const uint32_t n_pos = __ldg(&pr.count_pos), n_nrm = __ldg(&pr.count_nrm), n_uv = __ldg(&pr.count_uv);
-    float* po = pos_out + 9 * (size_t)g;
-    uint32_t* dout = data_out + 17 * (size_t)g;
+    // records are staged in shared memory (strides 9 and 17 words: conflict-free) and leave the CTA as one contiguous,
+    // 16-byte-vectorised run each — per-thread 36 B / 68 B records written directly touch every sector 9 / 17 times
+    float* po = sh_pos + 9u * threadIdx.x;
+    uint32_t* dout = sh_data + 17u * threadIdx.x;
     bool bad = false;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -372,6 +376,15 @@ __global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict
     dout[15] = __ldg(&pr.material);
     dout[16] = g;
     if (bad) atomicOr(flag, 1u);
+    __syncthreads();
+    const uint32_t live = min((uint32_t)kThreads, num_tris - g0);
+    float4* gp = reinterpret_cast<float4*>(pos_out + 9 * (size_t)g0);            // g0 * 36 B and g0 * 68 B are multiples of 16
+    uint4* gd = reinterpret_cast<uint4*>(data_out + 17 * (size_t)g0);
+    const uint32_t np4 = (9u * live) / 4u, nd4 = (17u * live) / 4u;
+    for (uint32_t i = threadIdx.x; i < np4; i += kThreads) gp[i] = reinterpret_cast<const float4*>(sh_pos)[i];
+    for (uint32_t i = threadIdx.x; i < nd4; i += kThreads) gd[i] = reinterpret_cast<const uint4*>(sh_data)[i];
+    for (uint32_t i = 4u * np4 + threadIdx.x; i < 9u * live; i += kThreads) pos_out[9 * (size_t)g0 + i] = sh_pos[i];
+    for (uint32_t i = 4u * nd4 + threadIdx.x; i < 17u * live; i += kThreads) data_out[17 * (size_t)g0 + i] = sh_data[i];
 }
 
 // ---------------------------------------------------------------------------------------------------------
