@@ -143,7 +143,7 @@ def run_reference(args, rank, world):
     mrays = tot_rays / tot_secs / 1e6
     frame_ms = tot_secs / args.steps * (cam.h / rows) * 1e3
     sample = "%d of %d rows (%d evenly spaced bands), all %d spp, per step" % (rows, cam.h, len(sample_bands(cam.h, n_rows)), spp)
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "Mrays/s", "value": round(mrays, 4), "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(frame_ms, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -341,14 +341,28 @@ def run_gpu(args, rank, world, local_rank):
             out["cpu_baseline"] = {"value": round(rays / secs / 1e6, 4), "unit": "Mrays/s", "cores": threads, "kind": "port",
                                    "sample": "%d of %d rows (%d evenly spaced bands), all %d spp; %.1f s" % (rows, cam.h, len(sample_bands(cam.h, n_rows)), spp, secs),
                                    "ms_per_frame_extrapolated": round(secs * cam.h / rows * 1e3, 1)}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     scene.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process' real stdout; everything else that writes to fd 1 while the bench runs
+    (NCCL prints its version banner there) has been pointed at stderr."""
+    with os.fdopen(os.dup(_RESULT_FD if _RESULT_FD is not None else 1), "w") as f:
+        f.write(line + "\n")
+
+
 def main():
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
