@@ -74,10 +74,13 @@ __device__ __forceinline__ bool queue_setup(const DevScene& sc, const Ray& r, Qu
 }
 __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const QueuedRay& e)
 {
-    q.a0[i] = make_float4(e.r.o.x, e.r.o.y, e.r.o.z, __uint_as_float(e.slot));
-    q.a1[i] = make_float4(e.r.d.x, e.r.d.y, e.r.d.z, __uint_as_float(e.c));
-    q.a2[i] = make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec));
-    q.a3[i] = make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.top));
+    // a0 / a1 carry what k_shade reads back (origin + slot, direction + top), a2 / a3 the iterator state only k_trace
+    // needs. Queues, hit records and the per-slot shading stack are written once and read once, gigabytes per launch:
+    // streaming (evict-first) accesses keep them from pushing the scene out of L2.
+    __stcs(q.a0 + i, make_float4(e.r.o.x, e.r.o.y, e.r.o.z, __uint_as_float(e.slot)));
+    __stcs(q.a1 + i, make_float4(e.r.d.x, e.r.d.y, e.r.d.z, __uint_as_float(e.top)));
+    __stcs(q.a2 + i, make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec)));
+    __stcs(q.a3 + i, make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.c)));
 }
 // Appends the rays of the lanes with `push` to the queue: one atomic per warp, order within the warp kept.
 __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, bool push, const QueuedRay& e)
@@ -165,7 +168,7 @@ k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam
                     }
                 }
             }
-            if (!push) ws.leaf[slot] = leaf;
+            if (!push) __stcs(ws.leaf + slot, leaf);
         }
         queue_push(ws.q[0], ws.counts, push, e);
     }
@@ -224,10 +227,10 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
             const uint32_t take = want < avail ? want : avail;
             if (!alive && (uint32_t)__popc(idle & lt_mask) < take) {
                 qi = next + __popc(idle & lt_mask);
-                const float4 a0 = __ldg(q.a0 + qi), a1 = __ldg(q.a1 + qi), a2 = __ldg(q.a2 + qi), a3 = __ldg(q.a3 + qi);
+                const float4 a0 = __ldcs(q.a0 + qi), a1 = __ldcs(q.a1 + qi), a2 = __ldcs(q.a2 + qi), a3 = __ldcs(q.a3 + qi);
                 ws.ro[lane] = a0; ws.rd[lane] = a1;
                 s.tx = a2.x; s.ty = a2.y; s.tz = a2.z; s.dx = a3.x; s.dy = a3.y; s.dz = a3.z;
-                s.c = __float_as_uint(a1.w); s.ec = __float_as_uint(a2.w);
+                s.c = __float_as_uint(a3.w); s.ec = __float_as_uint(a2.w);
                 trav_load_block<CSM>(sc, coarse, s);
                 best_t = inf; best_tri = kMiss;
                 alive = true;
@@ -298,7 +301,7 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
             __syncwarp();
         }
         if (done) {
-            hits[qi] = make_uint2(__float_as_uint(best_t), best_tri);
+            __stcs(hits + qi, make_uint2(__float_as_uint(best_t), best_tri));
             alive = false;
         }
     }
@@ -352,10 +355,10 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
         bool push = false;
         QueuedRay e;
         if (i < n) {
-            const float4 a0 = __ldg(qin.a0 + i), a1 = __ldg(qin.a1 + i);
-            const uint2 h = __ldg(ws.hits + i);
+            const float4 a0 = __ldcs(qin.a0 + i), a1 = __ldcs(qin.a1 + i);
+            const uint2 h = __ldcs(ws.hits + i);
             const uint32_t slot = __float_as_uint(a0.w);
-            uint32_t top = __float_as_uint(__ldg(&qin.a3[i].w));
+            uint32_t top = __float_as_uint(a1.w);
             Ray ray; ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
             const uint32_t sl = slot / wp.num_pixels, pl = slot - sl * wp.num_pixels;
             const uint32_t pixel = slot_pixel(wp, pl);
@@ -401,8 +404,8 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                     if (!(rnd[0] > transparency)) {          // scatter (stage3.zig:214-219)
                         ray.d = normalize(normal + unit_vector(rnd[1], rnd[2]));
                         const size_t k = (size_t)top * ws.cap + slot;
-                        ws.stack_e[k] = make_float4(emissive.x, emissive.y, emissive.z, albedo.x);
-                        ws.stack_a[k] = make_float2(albedo.y, albedo.z);
+                        __stcs(ws.stack_e + k, make_float4(emissive.x, emissive.y, emissive.z, albedo.x));
+                        __stcs(ws.stack_a + k, make_float2(albedo.y, albedo.z));
                         top += 1u;
                     }
                     if (bounce + 1u < wp.max_bounce) {       // depth - 1 > 0: the recursion goes on
@@ -413,7 +416,7 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                     }
                 }
             }
-            if (!push) ws.leaf[slot] = make_float4(leaf.x, leaf.y, leaf.z, __uint_as_float(top));
+            if (!push) __stcs(ws.leaf + slot, make_float4(leaf.x, leaf.y, leaf.z, __uint_as_float(top)));
         }
         queue_push(qout, ws.counts + bounce + 1u, push, e);
     }
@@ -435,12 +438,12 @@ k_accum(const __grid_constant__ WaveParams wp, const __grid_constant__ WaveScrat
     float4 a = accum[pixel];
     for (uint32_t sl = 0; sl < wp.ns; ++sl) {
         const uint32_t slot = sl * wp.num_pixels + pl;
-        const float4 lf = ws.leaf[slot];
+        const float4 lf = __ldcs(ws.leaf + slot);
         v3 value = mk(lf.x, lf.y, lf.z);
         for (uint32_t l = __float_as_uint(lf.w); l > 0u; --l) {
             const size_t k = (size_t)(l - 1u) * ws.cap + slot;
-            const float4 ea = ws.stack_e[k];
-            const float2 a2 = ws.stack_a[k];
+            const float4 ea = __ldcs(ws.stack_e + k);
+            const float2 a2 = __ldcs(ws.stack_a + k);
             value = mk(ea.x, ea.y, ea.z) + mk(ea.w, a2.x, a2.y) * value;
         }
         a.x = a.x + value.x; a.y = a.y + value.y; a.z = a.z + value.z;
