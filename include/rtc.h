@@ -288,7 +288,7 @@ typedef struct rtc_host_scene {
 /* loadGltfFile + loadCamera + loadMaterials + loadGeometry (src/stage1.zig:75,261,309,485) for a
  * .gltf (+ external buffers / PNG images / data: URIs) or .glb file. camera_name NULL = the first
  * camera; width/height 0 = not given (size rules of src/stage1.zig:322-342). PNG textures are
- * linearised like stb's stbi_loadf (pow(c/255, 2.2), alpha linear); JPEG is RTC_ERR_UNSUPPORTED. */
+ * linearised like stb's stbi_loadf (pow(c/255.0f, 2.2f) in double, alpha linear); JPEG is RTC_ERR_UNSUPPORTED. */
 int  rtc_gltf_load(const char* path, const char* camera_name, uint32_t width, uint32_t height,
                    int num_threads, rtc_host_scene* out);
 void rtc_host_scene_free(rtc_host_scene* scene);
@@ -296,7 +296,7 @@ void rtc_host_scene_free(rtc_host_scene* scene);
 /* The same stage1 with loadTriangles' per-triangle loop (src/stage1.zig:235-255: index fetch, node transform
  * of positions and normals, normalize, texcoords) ON the device: the file's buffers and one table row per
  * primitive are uploaded, one sm_100a kernel writes the soup; texture images go up as decoded 8-bit RGBA and are
- * linearised there (stb's pow(c/255, 2.2) table times the material factor, MASK / BLEND alpha; src/stage1.zig:427-472).
+ * linearised there (stb's pow(c/255.0f, 2.2f) table times the material factor, MASK / BLEND alpha; src/stage1.zig:427-472).
  * Needs a GPU; results are bit-identical to rtc_gltf_load's (an out-of-range vertex index is the same RTC_ERR_FORMAT).
  *
  * rtc_scene_create_from_gltf = loadGltfFile .. bakeInto (src/main.zig:104-118) in one call: the soup never

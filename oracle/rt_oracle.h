@@ -21,7 +21,10 @@
  * lanes, cross, length, getCellBbox, RGB size) is checked in tests/test_oracle_golden.py.
  * Everything else (Moller-Trumbore, textures, shading, tonemap, any image) has no
  * golden vector in the reference: for those pieces PARITY IS UNPINNED and this file is
- * the specification by construction from the cited lines.
+ * the specification by construction from the cited lines. The reference's one C unit
+ * (src/c_impl.c, stb) does build here (oracle/Makefile `ref` -> oracle/_ref/libc_libs.so);
+ * it pins texture decode + linearisation and PNG output (tests/test_ref_stb.py), which
+ * are inputs and outputs of the path, not the path.
  *
  * Arithmetic living in the un-vendored Zig standard library (version unpinned, 0.11 era):
  *   std.rand.DefaultPrng (Xoshiro256++), Random.float, Random.floatNorm (ziggurat):

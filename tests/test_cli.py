@@ -68,7 +68,7 @@ def test_gltf_loader_matches_oracle_stage1(orc, tmp_path, flavour):
     np.testing.assert_array_equal(m0.base_color.texels.reshape(3), np.float32([0.65, 0.05, 0.05]))
     np.testing.assert_array_equal(hs.materials[3].emissive.texels.reshape(3), np.float32([15, 15, 15]))
     img8 = gltf_io._to8(spec.materials[4].base_color.texels)                       # what the writer stored
-    lin = np.power((img8.astype(np.float32) / np.float32(255.0)).astype(np.float64), 2.2).astype(np.float32)
+    lin = np.power((img8.astype(np.float32) / np.float32(255.0)).astype(np.float64), float(np.float32(2.2))).astype(np.float32)   # stb: gamma is 2.2f
     assert np.array_equal(hs.materials[4].base_color.texels, lin)
     assert hs.materials[4].base_color.u_min == np.iinfo(np.int32).min                # REPEAT: no clamp range
     m5 = hs.materials[5]

@@ -1,0 +1,202 @@
+"""The host-side image code against THE REFERENCE'S OWN C UNIT: oracle/_ref/libc_libs.so is src/c_impl.c of the
+reference (the stb_image / stb_image_write instantiations build.zig:29-39 links as `c_libs`), compiled from where it
+lies by oracle/Makefile's `ref` target. What stage1 asks of it (src/stage1.zig:56-63:
+stbi_loadf_from_memory(ptr, len, &w, &h, &c, 4)) and what main asks of it (src/main.zig:130-135: stbi_write_png) is
+run here and compared bit for bit with the loader's texels and with the PNG reader / writer of librtc:
+  - colour channels linearised as pow(c/255, 2.2), alpha as c/255, for every PNG colour type and bit depth,
+    row filters, palette + tRNS, colour-key tRNS;
+  - a frame written by rtc_png_write decodes in stb to the same pixels; a frame written by stbi_write_png decodes in
+    rtc_png_read to the same pixels.
+Skipped when the reference's unit has not been built (no /root/reference on this machine and no prebuilt copy)."""
+import ctypes as C
+import json
+import os
+import struct
+import zlib
+
+import numpy as np
+import pytest
+
+from zig_raytracing_contest_b200 import gltf_io, rtc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libc_libs.so")
+
+
+@pytest.fixture(scope="module")
+def stb():
+    if not os.path.exists(REF_SO):
+        pytest.skip("oracle/_ref/libc_libs.so (the reference's stb unit) is not built on this machine")
+    L = C.CDLL(REF_SO)
+    L.stbi_loadf_from_memory.restype = C.POINTER(C.c_float)
+    L.stbi_loadf_from_memory.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
+    L.stbi_load_from_memory.restype = C.POINTER(C.c_uint8)
+    L.stbi_load_from_memory.argtypes = L.stbi_loadf_from_memory.argtypes
+    L.stbi_image_free.argtypes = [C.c_void_p]
+    L.stbi_image_free.restype = None
+    L.stbi_write_png.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    return L
+
+
+def _stb_load(L, data, req, as_float):
+    w, h, c = C.c_int(), C.c_int(), C.c_int()
+    fn = L.stbi_loadf_from_memory if as_float else L.stbi_load_from_memory
+    p = fn(data, len(data), C.byref(w), C.byref(h), C.byref(c), req)
+    assert p, "stb could not decode the image"
+    out = np.ctypeslib.as_array(p, (h.value, w.value, req)).copy()
+    L.stbi_image_free(p)
+    return out, c.value
+
+
+def _png(w, h, depth, ctype, samples, filters=None, plte=None, trns=None):
+    """A PNG of any colour type / bit depth from per-pixel sample values ([h, w, channels], already in range), with a
+    chosen filter type per row."""
+    ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    samples = np.asarray(samples).reshape(h, w * ch)
+    if depth == 16:
+        rows = samples.astype(">u2").view(np.uint8).reshape(h, -1)
+    elif depth == 8:
+        rows = samples.astype(np.uint8)
+    else:
+        per = 8 // depth
+        pad = (-samples.shape[1]) % per
+        s = np.pad(samples, ((0, 0), (0, pad))).astype(np.uint8).reshape(h, -1, per)
+        rows = np.zeros(s.shape[:2], np.uint8)
+        for k in range(per):
+            rows |= s[:, :, k] << (depth * (per - 1 - k))
+    bpp = max(1, ch * depth // 8)
+    raw = bytearray()
+    prev = np.zeros(rows.shape[1], np.int32)
+    for y in range(h):
+        cur = rows[y].astype(np.int32)
+        f = 0 if filters is None else filters[y % len(filters)]
+        left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])
+        ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])
+        if f == 0:
+            enc = cur
+        elif f == 1:
+            enc = cur - left
+        elif f == 2:
+            enc = cur - prev
+        elif f == 3:
+            enc = cur - ((left + prev) >> 1)
+        else:
+            p = left + prev - ul
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - ul)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
+            enc = cur - pred
+        raw.append(f)
+        raw.extend((enc & 255).astype(np.uint8).tobytes())
+        prev = cur
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 0))
+    if plte is not None:
+        out += chunk(b"PLTE", bytes(plte))
+    if trns is not None:
+        out += chunk(b"tRNS", bytes(trns))
+    return out + chunk(b"IDAT", zlib.compress(bytes(raw), 6)) + chunk(b"IEND", b"")
+
+
+def _cases():
+    rng = np.random.RandomState(11)
+    w, h = 13, 9
+    allf = [0, 1, 2, 3, 4]
+    yield "rgb8", _png(w, h, 8, 2, rng.randint(0, 256, (h, w, 3)), allf)
+    yield "rgba8", _png(w, h, 8, 6, rng.randint(0, 256, (h, w, 4)), allf)
+    yield "grey8", _png(w, h, 8, 0, rng.randint(0, 256, (h, w, 1)), allf)
+    yield "greya8", _png(w, h, 8, 4, rng.randint(0, 256, (h, w, 2)), allf)
+    yield "rgb16", _png(w, h, 16, 2, rng.randint(0, 65536, (h, w, 3)), allf)
+    yield "rgba16", _png(w, h, 16, 6, rng.randint(0, 65536, (h, w, 4)), allf)
+    yield "grey16", _png(w, h, 16, 0, rng.randint(0, 65536, (h, w, 1)), allf)
+    yield "greya16", _png(w, h, 16, 4, rng.randint(0, 65536, (h, w, 2)), allf)
+    for d in (1, 2, 4):
+        yield "grey%d" % d, _png(w, h, d, 0, rng.randint(0, 1 << d, (h, w, 1)), [0, 2])
+    pal = rng.randint(0, 256, 3 * 16)
+    yield "pal8", _png(w, h, 8, 3, rng.randint(0, 16, (h, w, 1)), allf, plte=pal)
+    yield "pal8_trns", _png(w, h, 8, 3, rng.randint(0, 16, (h, w, 1)), allf, plte=pal, trns=rng.randint(0, 256, 9))
+    for d in (1, 2, 4):
+        yield "pal%d" % d, _png(w, h, d, 3, rng.randint(0, min(16, 1 << d), (h, w, 1)), [0, 2], plte=pal)
+    key = rng.randint(0, 256, (h, w, 3))
+    key[2, 3] = key[5, 5] = (7, 200, 31)
+    yield "rgb8_colourkey", _png(w, h, 8, 2, key, allf, trns=struct.pack(">HHH", 7, 200, 31))
+    gk = rng.randint(0, 256, (h, w, 1))
+    gk[1, 1] = gk[4, 2] = 99
+    yield "grey8_colourkey", _png(w, h, 8, 0, gk, allf, trns=struct.pack(">H", 99))
+
+
+CASES = list(_cases())
+
+
+def _scene_with_images(tmp_path, names):
+    """One triangle, one camera, one BLEND material per image (base colour texture, factor 1)."""
+    pos = np.float32([[0, 0, 0], [1, 0, 0], [0, 1, 0]])
+    nrm = np.float32([[0, 0, 1]] * 3)
+    idx = np.uint16([0, 1, 2, 0])
+    blob = pos.tobytes() + nrm.tobytes() + idx.tobytes()
+    open(str(tmp_path / "s.bin"), "wb").write(blob)
+    doc = {"asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0, 1]}],
+           "nodes": [{"mesh": 0}, {"camera": 0, "translation": [0, 0, 3]}],
+           "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1}, "indices": 2, "material": 0}]}],
+           "cameras": [{"type": "perspective", "perspective": {"yfov": 0.8, "aspectRatio": 1.0, "znear": 0.1}}],
+           "buffers": [{"uri": "s.bin", "byteLength": len(blob)}],
+           "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": 36}, {"buffer": 0, "byteOffset": 36, "byteLength": 36},
+                           {"buffer": 0, "byteOffset": 72, "byteLength": 6}],
+           "accessors": [{"bufferView": 0, "componentType": 5126, "count": 3, "type": "VEC3"},
+                         {"bufferView": 1, "componentType": 5126, "count": 3, "type": "VEC3"},
+                         {"bufferView": 2, "componentType": 5123, "count": 3, "type": "SCALAR"}],
+           "images": [{"uri": n + ".png"} for n in names],
+           "textures": [{"source": i} for i in range(len(names))],
+           "materials": [{"alphaMode": "BLEND", "pbrMetallicRoughness": {"baseColorTexture": {"index": i}}} for i in range(len(names))]}
+    path = str(tmp_path / "s.gltf")
+    json.dump(doc, open(path, "w"))
+    return path
+
+
+def test_loader_texels_equal_stbi_loadf(stb, tmp_path):
+    for name, data in CASES:
+        open(str(tmp_path / (name + ".png")), "wb").write(data)
+    hs = rtc.HostSceneData(_scene_with_images(tmp_path, [n for n, _ in CASES]), height=8, num_threads=3)
+    for i, (name, data) in enumerate(CASES):
+        want, actual_c = _stb_load(stb, data, 4, True)                # what src/stage1.zig:56-63 gets
+        m = hs.materials[i]
+        assert m.base_color.texels.shape == want[:, :, :3].shape, name
+        assert np.array_equal(m.base_color.texels.view(np.uint32), want[:, :, :3].view(np.uint32)), name
+        if actual_c in (2, 4):                                        # src/stage1.zig:455: only images that carry alpha
+            assert np.array_equal(m.transparency.texels[:, :, 0].view(np.uint32), want[:, :, 3].view(np.uint32)), name
+        else:
+            assert m.transparency.texels.shape == (1, 1, 1) and m.transparency.texels[0, 0, 0] == 1.0, name
+
+
+def test_png_reader_equals_stbi_load(stb, tmp_path):
+    for name, data in CASES:
+        path = str(tmp_path / (name + ".png"))
+        open(path, "wb").write(data)
+        want, _ = _stb_load(stb, data, 3, False)
+        assert np.array_equal(rtc.png_read(path), want), name
+
+
+def test_png_writer_and_stbi_write_png_are_interchangeable(stb, tmp_path):
+    rng = np.random.RandomState(5)
+    for (h, w) in ((1, 1), (7, 5), (270, 480), (700, 1100)):           # the last one spans several deflate slices
+        img = rng.randint(0, 256, (h, w, 3)).astype(np.uint8)
+        img[h // 2:] = (np.linspace(0, 255, w)[None, :, None]).astype(np.uint8)
+        mine = str(tmp_path / "mine.png")
+        rtc.png_write(mine, img)
+        got, c = _stb_load(stb, open(mine, "rb").read(), 3, False)
+        assert c == 3 and np.array_equal(got, img)
+        theirs = str(tmp_path / "theirs.png")
+        assert stb.stbi_write_png(theirs.encode(), w, h, 3, img.ctypes.data, 3 * w) == 1     # src/main.zig:130-139
+        assert np.array_equal(rtc.png_read(theirs), img)
+
+
+def test_texture_images_of_the_test_scenes_equal_stb(stb, tmp_path):
+    """The PNGs the procedural scenes' writer stores (what every other loader test reads)."""
+    rng = np.random.RandomState(2)
+    for c in (1, 2, 3, 4):
+        data = gltf_io.png_encode(rng.randint(0, 256, (17, 31, c)).astype(np.uint8))
+        path = str(tmp_path / ("c%d.png" % c))
+        open(path, "wb").write(data)
+        want, actual = _stb_load(stb, data, 3, False)
+        assert actual == c and np.array_equal(rtc.png_read(path), want)

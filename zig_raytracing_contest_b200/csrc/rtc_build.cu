@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(kThreads) k_assemble(const uint8_t* __restrict
 // ---------------------------------------------------------------------------------------------------------
 // Texel linearisation (stb_image.h:1856-1877 + src/stage1.zig:433-440, 455-468) on the device: the decoded
 // 8-bit RGBA image goes up once (4 B/texel instead of 12-16 B of floats), every texture made from it is one
-// launch. lut = pow(c/255, 2.2) evaluated in double on the host and rounded to float (256 entries); the
+// launch. lut = pow(c/255.0f, 2.2f) evaluated in double on the host and rounded to float (256 entries); the
 // per-texel arithmetic is one fp32 multiply by the material's factor (RGB), c/255 in fp32 (BLEND) or a compare
 // of that against alphaCutoff (MASK) — bit-identical to the host loader's.
 __global__ void __launch_bounds__(kThreads) k_texels_rgb(const uchar4* __restrict__ img, uint32_t n, const float* __restrict__ lut,

@@ -209,11 +209,14 @@ void fill_parents(const Json& nodes, std::vector<int>& parent, size_t node, int 
     }
 }
 
-// stb_image.h:1856-1877 (stbi__ldr_to_hdr): colour channels pow(c/255, 2.2) * 1.0 evaluated in double and
+// stb_image.h:1856-1877 (stbi__ldr_to_hdr): colour channels pow(c/255.0f, 2.2f) * 1.0f evaluated in double and
 // rounded to float; the alpha channel is c/255 in float.
 void linear_lut(float lut[256])
 {
-    for (int i = 0; i < 256; ++i) lut[i] = (float)(pow((double)((float)i / 255.0f), 2.2) * 1.0);
+    // stb_image.h:1571,1867: the gamma and scale are FLOAT statics (2.2f, 1.0f) promoted to double inside pow —
+    // pow(c/255.0f, (double)2.2f), not pow(., 2.2); pinned against the reference's own unit in tests/test_ref_stb.py
+    const float gamma = 2.2f, scale = 1.0f;
+    for (int i = 0; i < 256; ++i) lut[i] = (float)(pow((double)((float)i / 255.0f), (double)gamma) * (double)scale);
 }
 void linearise(const rtc_host::DecodedImage& src, Image& dst)
 {

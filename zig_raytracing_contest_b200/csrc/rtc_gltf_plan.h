@@ -65,7 +65,7 @@ struct RtcHostSceneOwner {
 };
 
 // A texture whose texels are produced on the device from a decoded 8-bit image (rtc_build.cu: k_texels):
-//   RGB         rgb = lut[c] * k   (stb's pow(c/255, 2.2) table, times the material's factor; stage1.zig:427-446)
+//   RGB         rgb = lut[c] * k   (stb's pow(c/255.0f, 2.2f) table, times the material's factor; stage1.zig:427-446)
 //   ALPHA       a = c/255          (alphaMode BLEND; stage1.zig:448-472)
 //   ALPHA_MASK  a > k[0] ? 1 : 0   (alphaMode MASK, k[0] = alphaCutoff)
 // The rtc_material's texture has texels == nullptr; w, h, channels and the clamp range are set.
