@@ -43,6 +43,17 @@ def test_device_assembly_matches_host_loader(tmp_path, flavour, scene):
     _same_host_scene(host, dev)
 
 
+def test_jpeg_textures_through_the_device_path(tmp_path):
+    """JPEG-textured materials: decoded on the host (csrc/rtc_jpeg.h), linearised on the device."""
+    pytest.importorskip("PIL.Image")
+    from test_ref_stb import _jpeg_cases, _scene_with_images
+    cases = [c for c in _jpeg_cases() if "131x67" in c[0] or "restart" in c[0]]
+    for name, data in cases:
+        open(str(tmp_path / (name + ".png")), "wb").write(data)
+    path = _scene_with_images(tmp_path, [n for n, _ in cases])
+    _same_host_scene(rtc.HostSceneData(path, height=8, num_threads=2), rtc.HostSceneData(path, height=8, num_threads=2, device=0))
+
+
 def test_device_assembly_index_types_strides_alignment(orc, tmp_path):
     path, doc, want = handmade(tmp_path, np.random.default_rng(5))
     host = rtc.HostSceneData(path, height=32)

@@ -200,3 +200,80 @@ def test_texture_images_of_the_test_scenes_equal_stb(stb, tmp_path):
         open(path, "wb").write(data)
         want, actual = _stb_load(stb, data, 3, False)
         assert actual == c and np.array_equal(rtc.png_read(path), want)
+
+
+def _jpeg_cases():
+    PIL = pytest.importorskip("PIL.Image")
+    import io
+    rng = np.random.RandomState(21)
+
+    def picture(h, w):
+        y, x = np.mgrid[0:h, 0:w]
+        img = np.stack([128 + 100 * np.sin(x / 7.0) * np.cos(y / 5.0), (x * 255.0 / max(1, w - 1)), (y * 255.0 / max(1, h - 1))], axis=2)
+        img += rng.normal(0, 12, img.shape)
+        img[h // 3:h // 2, w // 4:w // 2] = (250, 10, 10)                 # hard edges: chroma upsampling shows
+        return np.clip(img, 0, 255).astype(np.uint8)
+
+    def enc(img, mode="RGB", **kw):
+        b = io.BytesIO()
+        PIL.fromarray(img if mode == "RGB" else img[:, :, 0], mode).save(b, "JPEG", **kw)
+        return b.getvalue()
+    for (h, w) in ((1, 1), (9, 13), (33, 17), (48, 64), (67, 131)):
+        img = picture(h, w)
+        for sub in (0, 1, 2):
+            yield "baseline_%dx%d_sub%d" % (w, h, sub), enc(img, quality=80, subsampling=sub)
+            yield "progressive_%dx%d_sub%d" % (w, h, sub), enc(img, quality=70, subsampling=sub, progressive=True)
+        yield "grey_%dx%d" % (w, h), enc(img, "L", quality=85)
+        yield "grey_progressive_%dx%d" % (w, h), enc(img, "L", quality=60, progressive=True)
+    img = picture(120, 200)
+    yield "optimized_q30", enc(img, quality=30, optimize=True)
+    yield "q100", enc(img, quality=100, subsampling=0)
+    yield "q5", enc(img, quality=5, subsampling=2)
+    try:
+        yield "restart_blocks", enc(img, quality=75, subsampling=2, restart_marker_blocks=3)
+        yield "restart_rows_progressive", enc(img, quality=75, subsampling=1, restart_marker_rows=1, progressive=True)
+    except TypeError:
+        pass
+    try:
+        import cv2
+        bgr = np.ascontiguousarray(img[:, :, ::-1])
+        for name, sf in (("411", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_411), ("440", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_440)):
+            ok, buf = cv2.imencode(".jpg", bgr, [cv2.IMWRITE_JPEG_QUALITY, 85, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, sf, cv2.IMWRITE_JPEG_RST_INTERVAL, 5])
+            if ok:
+                yield "cv2_" + name, buf.tobytes()
+    except (ImportError, AttributeError):
+        pass
+
+
+def test_jpeg_textures_equal_stbi_loadf(stb, tmp_path):
+    """JPEG textures through the loader against the reference's stb: baseline and progressive, 4:4:4 / 4:2:2 / 4:2:0 /
+    4:1:1 / 4:4:0, greyscale, custom Huffman tables, restart intervals, sizes that are not multiples of the MCU."""
+    cases = list(_jpeg_cases())
+    assert len(cases) > 40
+    for name, data in cases:
+        open(str(tmp_path / (name + ".png")), "wb").write(data)          # the loader goes by content, not by extension
+    hs = rtc.HostSceneData(_scene_with_images(tmp_path, [n for n, _ in cases]), height=8, num_threads=4)
+    for i, (name, data) in enumerate(cases):
+        want, actual_c = _stb_load(stb, data, 4, True)
+        m = hs.materials[i]
+        assert m.base_color.texels.shape == want[:, :, :3].shape, name
+        diff = m.base_color.texels.view(np.uint32) != want[:, :, :3].view(np.uint32)
+        assert not diff.any(), (name, int(diff.sum()), diff.shape)
+        assert m.transparency.texels.shape == (1, 1, 1), name             # JPEG has no alpha (actual_c 3 or 1)
+
+
+def test_unsupported_jpegs_are_reported(tmp_path):
+    PIL = pytest.importorskip("PIL.Image")
+    import io
+    from zig_raytracing_contest_b200 import abi
+    b = io.BytesIO()
+    PIL.fromarray(np.zeros((8, 8, 4), np.uint8), "CMYK").save(b, "JPEG")
+    open(str(tmp_path / "cmyk.png"), "wb").write(b.getvalue())
+    with pytest.raises(rtc.RtcError) as e:
+        rtc.HostSceneData(_scene_with_images(tmp_path, ["cmyk"]), height=8)
+    assert e.value.code == abi.RTC_ERR_UNSUPPORTED and "CMYK" in str(e.value)
+    good = io.BytesIO()
+    PIL.fromarray(np.full((16, 16, 3), 90, np.uint8), "RGB").save(good, "JPEG")
+    open(str(tmp_path / "cut.png"), "wb").write(good.getvalue()[:40])               # cut inside the tables
+    with pytest.raises(rtc.RtcError):
+        rtc.HostSceneData(_scene_with_images(tmp_path, ["cut"]), height=8)

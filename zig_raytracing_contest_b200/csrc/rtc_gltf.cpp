@@ -9,6 +9,7 @@
 // vertex the render path sees, and must evaluate like the reference's fp32 code.
 #include "../../include/rtc.h"
 #include "rtc_gltf_plan.h"
+#include "rtc_jpeg.h"
 #include "rtc_json.h"
 #include "rtc_png.h"
 
@@ -307,15 +308,14 @@ void load_asset(const std::string& path, int threads, Asset& a)
                     if (im.has("bufferView")) bytes = view_bytes(a, im.integer("bufferView", -1));
                     else if (im.has("uri")) { owned = load_uri(a.dir, im.string("uri", "")); bytes = BufferSpan{ owned.data(), owned.size() }; }
                     else fail(RTC_ERR_FORMAT, "glTF: image without bufferView or uri");
-                    if (bytes.n >= 3 && bytes.p[0] == 0xFF && bytes.p[1] == 0xD8)
-                        fail(RTC_ERR_UNSUPPORTED, "glTF: image " + std::to_string(i) + " is a JPEG; this host decodes PNG textures only");
                     try {
+                        const bool jpg = rtc_host::is_jpeg(bytes.p, bytes.n);
                         if (a.defer_texels) {
-                            rtc_host::DecodedImage dec = rtc_host::png_decode(bytes.p, bytes.n);
+                            rtc_host::DecodedImage dec = jpg ? rtc_host::jpeg_decode(bytes.p, bytes.n) : rtc_host::png_decode(bytes.p, bytes.n);
                             Image& im8 = a.images[i];
                             im8.w = dec.w; im8.h = dec.h; im8.actual_c = dec.actual_c; im8.rgba8 = std::move(dec.rgba);
                         } else
-                            linearise(rtc_host::png_decode(bytes.p, bytes.n), a.images[i]);
+                            linearise(jpg ? rtc_host::jpeg_decode(bytes.p, bytes.n) : rtc_host::png_decode(bytes.p, bytes.n), a.images[i]);
                     } catch (const std::runtime_error& e) {
                         fail(RTC_ERR_UNSUPPORTED, "glTF: image " + std::to_string(i) + ": " + e.what());
                     }
