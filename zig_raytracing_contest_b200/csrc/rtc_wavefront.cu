@@ -43,7 +43,10 @@ static constexpr uint32_t kFull = 0xFFFFFFFFu;
 #endif
 
 static constexpr int kMaxStep = RTC_KMAXSTEP;        // DDA steps a lane may take per round before the pooled triangle pass
-static constexpr uint32_t kChunk = 64;               // queue entries a warp reserves per atomic
+#ifndef RTC_CHUNK
+#define RTC_CHUNK 64
+#endif
+static constexpr uint32_t kChunk = RTC_CHUNK;        // queue entries a warp reserves per atomic
 
 // ---------------------------------------------------------------------------------------------------------
 // Ray queue entry (64 B, SoA over four float4 arrays): the ray and its DDA set-up.
