@@ -277,3 +277,30 @@ def test_unsupported_jpegs_are_reported(tmp_path):
     open(str(tmp_path / "cut.png"), "wb").write(good.getvalue()[:40])               # cut inside the tables
     with pytest.raises(rtc.RtcError):
         rtc.HostSceneData(_scene_with_images(tmp_path, ["cut"]), height=8)
+
+
+def test_stb_compatible_writer_is_byte_identical(stb, tmp_path, monkeypatch):
+    """RTC_PNG_STB=1: the file is the one stbi_write_png (src/main.zig:130-135) writes, byte for byte — filter choice per
+    row, stb's own deflate (hash buckets, lazy matching, fixed Huffman block, stored-block fallback), Adler, CRCs."""
+    rng = np.random.RandomState(9)
+    monkeypatch.setenv("RTC_PNG_STB", "1")
+    frames = []
+    for (h, w) in ((1, 1), (2, 3), (5, 7), (64, 64), (200, 333)):
+        frames.append(rng.randint(0, 256, (h, w, 3)).astype(np.uint8))                           # noise: stored blocks
+        y, x = np.mgrid[0:h, 0:w]
+        g = np.stack([x * 255 // max(1, w - 1), y * 255 // max(1, h - 1), (x + y) % 256], axis=2).astype(np.uint8)
+        frames.append(g)                                                                          # gradients: filters matter
+        frames.append(np.full((h, w, 3), 77, np.uint8))                                           # flat: long matches
+        frames.append(np.where(rng.rand(h, w, 1) < 0.02, rng.randint(0, 256, (h, w, 3)), g).astype(np.uint8))
+    tile = rng.randint(0, 256, (16, 16, 3)).astype(np.uint8)
+    frames.append(np.tile(tile, (40, 50, 1)))                                                     # repeats beyond the bucket depth and the window
+    frames.append((np.clip(rng.normal(128, 6, (300, 400, 3)), 0, 255)).astype(np.uint8))         # what a rendered frame looks like
+    for k, img in enumerate(frames):
+        img = np.ascontiguousarray(img)
+        h, w, _ = img.shape
+        mine, theirs = str(tmp_path / "mine.png"), str(tmp_path / "theirs.png")
+        rtc.png_write(mine, img)
+        assert stb.stbi_write_png(theirs.encode(), w, h, 3, img.ctypes.data, 3 * w) == 1
+        a, b = open(mine, "rb").read(), open(theirs, "rb").read()
+        assert a == b, (k, img.shape, len(a), len(b))
+        assert np.array_equal(rtc.png_read(mine), img)

@@ -803,7 +803,11 @@ int rtc_png_write(const char* path, uint32_t w, uint32_t h, const uint8_t* rgb)
     return guarded([&] {
         int threads = (int)std::thread::hardware_concurrency();
         if (const char* e = getenv("RTC_PNG_THREADS")) threads = atoi(e);
-        const std::vector<uint8_t> png = rtc_host::png_encode_rgb8(w, h, rgb, threads);
+        // RTC_PNG_STB=1: the file stbi_write_png would write, byte for byte (single-threaded); default: same pixels, zlib
+        // slices on all threads
+        const char* stb_mode = getenv("RTC_PNG_STB");
+        const std::vector<uint8_t> png = stb_mode && stb_mode[0] == '1' ? rtc_host::png_encode_rgb8_stb(w, h, rgb)
+                                                                        : rtc_host::png_encode_rgb8(w, h, rgb, threads);
         FILE* f = fopen(path, "wb");
         if (!f) fail(RTC_ERR_IO, std::string("WritePngFail: cannot open '") + path + "'");
         const size_t n = fwrite(png.data(), 1, png.size(), f);

@@ -11,6 +11,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -89,6 +90,150 @@ inline std::vector<uint8_t> png_encode_rgb8(uint32_t w, uint32_t h, const uint8_
         memcpy(row + 1, rgb + (size_t)y * 3 * w, 3 * (size_t)w);
     }
     const std::vector<uint8_t> z = zlib_parallel(raw.data(), raw.size(), threads);
+    std::vector<uint8_t> out = { 0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n' };
+    std::vector<uint8_t> ihdr;
+    be32(ihdr, w); be32(ihdr, h);
+    ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);
+    png_chunk(out, "IHDR", ihdr.data(), ihdr.size());
+    png_chunk(out, "IDAT", z.data(), z.size());
+    png_chunk(out, "IEND", nullptr, 0);
+    return out;
+}
+
+// ---- the reference's own file, byte for byte ---------------------------------------------------------------------
+// stbi_write_png (stb_image_write.h:1092-1229) restated: per row the filter (none / sub / up / average / paeth; the
+// first row's variants) with the smallest sum of |signed byte|, first winner kept; then stb's own deflate
+// (stb_image_write.h:859-1021): one fixed-Huffman block, 16384 hash buckets keyed on 3 bytes, each bucket holding at
+// most 2*quality positions (the older half dropped when full), the LAST longest match of at least 3 bytes inside the
+// 32 KiB window, abandoned for a literal when the next byte starts a longer one; stored blocks if that came out
+// larger. Pinned against the reference's unit in tests/test_ref_stb.py. Single-threaded by construction; the default
+// writer (zlib slices on all threads) produces the same pixels in a fraction of the time.
+inline std::vector<uint8_t> stb_zlib_compress(const uint8_t* data, int n, int quality)
+{
+    static const uint16_t len_base[] = { 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258, 259 };
+    static const uint8_t len_extra[] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
+    static const uint16_t dist_base[] = { 1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145,
+                                          8193, 12289, 16385, 24577, 32768 };
+    static const uint8_t dist_extra[] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
+    const int kBuckets = 16384;
+    if (quality < 5) quality = 5;
+    std::vector<uint8_t> out = { 0x78, 0x5e };
+    uint32_t bitbuf = 0;
+    int bitcount = 0;
+    auto add = [&](uint32_t code, int nbits) {
+        bitbuf |= code << bitcount; bitcount += nbits;
+        while (bitcount >= 8) { out.push_back((uint8_t)bitbuf); bitbuf >>= 8; bitcount -= 8; }
+    };
+    auto rev = [](int code, int nbits) { int r = 0; while (nbits--) { r = (r << 1) | (code & 1); code >>= 1; } return r; };
+    auto symbol = [&](int v) {                             // the fixed literal/length code of RFC 1951 3.2.6
+        if (v <= 143) add((uint32_t)rev(0x30 + v, 8), 8);
+        else if (v <= 255) add((uint32_t)rev(0x190 + v - 144, 9), 9);
+        else if (v <= 279) add((uint32_t)rev(v - 256, 7), 7);
+        else add((uint32_t)rev(0xc0 + v - 280, 8), 8);
+    };
+    auto hash3 = [&](int i) {
+        uint32_t h = (uint32_t)data[i] + ((uint32_t)data[i + 1] << 8) + ((uint32_t)data[i + 2] << 16);
+        h ^= h << 3; h += h >> 5; h ^= h << 4; h += h >> 17; h ^= h << 25; h += h >> 6;
+        return (int)(h & (uint32_t)(kBuckets - 1));
+    };
+    auto run = [&](int a, int b, int limit) { int k = 0; while (k < limit && k < 258 && data[a + k] == data[b + k]) ++k; return k; };
+    add(1, 1);                                             // BFINAL
+    add(1, 2);                                             // BTYPE = fixed Huffman
+    std::vector<std::vector<int>> buckets((size_t)kBuckets);
+    int i = 0;
+    while (i < n - 3) {
+        std::vector<int>& bk = buckets[(size_t)hash3(i)];
+        int best = 3, where = -1;
+        for (int pos : bk)
+            if (pos > i - 32768) { const int d = run(pos, i, n - i); if (d >= best) { best = d; where = pos; } }
+        if ((int)bk.size() == 2 * quality) bk.erase(bk.begin(), bk.begin() + quality);
+        bk.push_back(i);
+        if (where >= 0) {
+            const std::vector<int>& nx = buckets[(size_t)hash3(i + 1)];
+            for (int pos : nx)
+                if (pos > i - 32767 && run(pos, i + 1, n - i - 1) > best) { where = -1; break; }
+        }
+        if (where >= 0) {
+            const int d = i - where;
+            int j = 0;
+            while (best > len_base[j + 1] - 1) ++j;
+            symbol(j + 257);
+            if (len_extra[j]) add((uint32_t)(best - len_base[j]), len_extra[j]);
+            j = 0;
+            while (d > dist_base[j + 1] - 1) ++j;
+            add((uint32_t)rev(j, 5), 5);
+            if (dist_extra[j]) add((uint32_t)(d - dist_base[j]), dist_extra[j]);
+            i += best;
+        } else {
+            symbol(data[i]);
+            ++i;
+        }
+    }
+    for (; i < n; ++i) symbol(data[i]);
+    symbol(256);
+    while (bitcount) add(0, 1);
+    if ((long long)out.size() > (long long)n + 2 + ((n + 32766) / 32767) * 5) {          // stored blocks came out smaller
+        out.resize(2);
+        for (int j = 0; j < n;) {
+            int len = n - j;
+            if (len > 32767) len = 32767;
+            out.push_back((uint8_t)(n - j == len));
+            out.push_back((uint8_t)len); out.push_back((uint8_t)(len >> 8));
+            out.push_back((uint8_t)~len); out.push_back((uint8_t)(~len >> 8));
+            out.insert(out.end(), data + j, data + j + len);
+            j += len;
+        }
+    }
+    be32(out, (uint32_t)adler32(1L, data, (uInt)n));
+    return out;
+}
+
+inline std::vector<uint8_t> png_encode_rgb8_stb(uint32_t w, uint32_t h, const uint8_t* rgb)
+{
+    const int n = 3, row = (int)w * n;
+    if ((uint64_t)h * ((uint64_t)row + 1) > 0x7fffffffull) throw std::runtime_error("PNG: frame too large for the stb-compatible writer");
+    std::vector<uint8_t> filt((size_t)h * ((size_t)row + 1));
+    std::vector<int8_t> line((size_t)row), keep((size_t)row);
+    auto paeth = [](int a, int b, int c) {
+        const int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+        return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+    };
+    auto encode = [&](uint32_t y, int filter, int8_t* o) {
+        static const int first_row[5] = { 0, 1, 0, 5, 6 };
+        const int type = y ? filter : first_row[filter];
+        const uint8_t* z = rgb + (size_t)y * row;
+        const uint8_t* up = z - row;
+        if (type == 0) { memcpy(o, z, (size_t)row); return; }
+        for (int i = 0; i < n; ++i)
+            switch (type) {
+                case 2: o[i] = (int8_t)(z[i] - up[i]); break;
+                case 3: o[i] = (int8_t)(z[i] - (up[i] >> 1)); break;
+                case 4: o[i] = (int8_t)(z[i] - paeth(0, up[i], 0)); break;
+                default: o[i] = (int8_t)z[i]; break;
+            }
+        for (int i = n; i < row; ++i)
+            switch (type) {
+                case 1: o[i] = (int8_t)(z[i] - z[i - n]); break;
+                case 2: o[i] = (int8_t)(z[i] - up[i]); break;
+                case 3: o[i] = (int8_t)(z[i] - ((z[i - n] + up[i]) >> 1)); break;
+                case 4: o[i] = (int8_t)(z[i] - paeth(z[i - n], up[i], up[i - n])); break;
+                case 5: o[i] = (int8_t)(z[i] - (z[i - n] >> 1)); break;
+                default: o[i] = (int8_t)(z[i] - paeth(z[i - n], 0, 0)); break;
+            }
+    };
+    for (uint32_t y = 0; y < h; ++y) {
+        int best = 0, best_val = 0x7fffffff;
+        for (int f = 0; f < 5; ++f) {
+            encode(y, f, line.data());
+            int est = 0;
+            for (int i = 0; i < row; ++i) est += abs((int)line[(size_t)i]);
+            if (est < best_val) { best_val = est; best = f; keep.swap(line); }
+        }
+        uint8_t* dst = filt.data() + (size_t)y * ((size_t)row + 1);
+        dst[0] = (uint8_t)best;
+        memcpy(dst + 1, keep.data(), (size_t)row);
+    }
+    const std::vector<uint8_t> z = stb_zlib_compress(filt.data(), (int)filt.size(), 8);
     std::vector<uint8_t> out = { 0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n' };
     std::vector<uint8_t> ihdr;
     be32(ihdr, w); be32(ihdr, h);
