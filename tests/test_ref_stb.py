@@ -48,55 +48,71 @@ def _stb_load(L, data, req, as_float):
     return out, c.value
 
 
-def _png(w, h, depth, ctype, samples, filters=None, plte=None, trns=None):
+def _png(w, h, depth, ctype, samples, filters=None, plte=None, trns=None, adam7=False):
     """A PNG of any colour type / bit depth from per-pixel sample values ([h, w, channels], already in range), with a
-    chosen filter type per row."""
+    chosen filter type per row; adam7 = the seven-pass interlace (every pass filtered as an image of its own)."""
     ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
-    samples = np.asarray(samples).reshape(h, w * ch)
-    if depth == 16:
-        rows = samples.astype(">u2").view(np.uint8).reshape(h, -1)
-    elif depth == 8:
-        rows = samples.astype(np.uint8)
-    else:
+    samples = np.asarray(samples).reshape(h, w, ch)
+    bpp = max(1, ch * depth // 8)
+
+    def rows_of(sub):
+        hh, ww, _ = sub.shape
+        flat = sub.reshape(hh, ww * ch)
+        if depth == 16:
+            return flat.astype(">u2").view(np.uint8).reshape(hh, -1)
+        if depth == 8:
+            return flat.astype(np.uint8)
         per = 8 // depth
-        pad = (-samples.shape[1]) % per
-        s = np.pad(samples, ((0, 0), (0, pad))).astype(np.uint8).reshape(h, -1, per)
+        pad = (-flat.shape[1]) % per
+        s = np.pad(flat, ((0, 0), (0, pad))).astype(np.uint8).reshape(hh, -1, per)
         rows = np.zeros(s.shape[:2], np.uint8)
         for k in range(per):
             rows |= s[:, :, k] << (depth * (per - 1 - k))
-    bpp = max(1, ch * depth // 8)
-    raw = bytearray()
-    prev = np.zeros(rows.shape[1], np.int32)
-    for y in range(h):
-        cur = rows[y].astype(np.int32)
-        f = 0 if filters is None else filters[y % len(filters)]
-        left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])
-        ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])
-        if f == 0:
-            enc = cur
-        elif f == 1:
-            enc = cur - left
-        elif f == 2:
-            enc = cur - prev
-        elif f == 3:
-            enc = cur - ((left + prev) >> 1)
-        else:
-            p = left + prev - ul
-            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - ul)
-            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
-            enc = cur - pred
-        raw.append(f)
-        raw.extend((enc & 255).astype(np.uint8).tobytes())
-        prev = cur
+        return rows
+
+    def filtered(rows):
+        raw = bytearray()
+        prev = np.zeros(rows.shape[1], np.int32)
+        for y in range(rows.shape[0]):
+            cur = rows[y].astype(np.int32)
+            f = 0 if filters is None else filters[y % len(filters)]
+            left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])[:len(cur)]
+            ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])[:len(cur)]
+            if f == 0:
+                enc = cur
+            elif f == 1:
+                enc = cur - left
+            elif f == 2:
+                enc = cur - prev
+            elif f == 3:
+                enc = cur - ((left + prev) >> 1)
+            else:
+                p = left + prev - ul
+                pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - ul)
+                pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
+                enc = cur - pred
+            raw.append(f)
+            raw.extend((enc & 255).astype(np.uint8).tobytes())
+            prev = cur
+        return bytes(raw)
+
+    if adam7:
+        raw = b""
+        for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+            sub = samples[y0::dy, x0::dx]
+            if sub.shape[0] and sub.shape[1]:
+                raw += filtered(rows_of(sub))
+    else:
+        raw = filtered(rows_of(samples))
 
     def chunk(tag, data):
         return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
-    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 0))
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 1 if adam7 else 0))
     if plte is not None:
         out += chunk(b"PLTE", bytes(plte))
     if trns is not None:
         out += chunk(b"tRNS", bytes(trns))
-    return out + chunk(b"IDAT", zlib.compress(bytes(raw), 6)) + chunk(b"IEND", b"")
+    return out + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b"")
 
 
 def _cases():
@@ -124,6 +140,23 @@ def _cases():
     gk = rng.randint(0, 256, (h, w, 1))
     gk[1, 1] = gk[4, 2] = 99
     yield "grey8_colourkey", _png(w, h, 8, 0, gk, allf, trns=struct.pack(">H", 99))
+    k16 = rng.randint(0, 65536, (h, w, 3))
+    k16[3, 3] = k16[0, 12] = (513, 40000, 77)
+    k16[6, 1] = (513 + 1, 40000, 77)                                   # same high bytes, different low byte: not the key
+    yield "rgb16_colourkey", _png(w, h, 16, 2, k16, allf, trns=struct.pack(">HHH", 513, 40000, 77))
+    g16 = rng.randint(0, 65536, (h, w, 1))
+    g16[2, 2] = 0x1234
+    g16[2, 3] = 0x1235
+    yield "grey16_colourkey", _png(w, h, 16, 0, g16, allf, trns=struct.pack(">H", 0x1234))
+    g4 = rng.randint(0, 16, (h, w, 1))
+    yield "grey4_colourkey", _png(w, h, 4, 0, g4, [0, 1, 4], trns=struct.pack(">H", 5))
+    g2 = rng.randint(0, 4, (h, w, 1))
+    yield "grey2_colourkey", _png(w, h, 2, 0, g2, [0, 2], trns=struct.pack(">H", 2))
+    for (hh, ww) in ((1, 1), (2, 3), (5, 4), (9, 13), (16, 16), (33, 21)):
+        yield "adam7_rgb8_%dx%d" % (ww, hh), _png(ww, hh, 8, 2, rng.randint(0, 256, (hh, ww, 3)), allf, adam7=True)
+        yield "adam7_rgba16_%dx%d" % (ww, hh), _png(ww, hh, 16, 6, rng.randint(0, 65536, (hh, ww, 4)), allf, adam7=True)
+        yield "adam7_grey1_%dx%d" % (ww, hh), _png(ww, hh, 1, 0, rng.randint(0, 2, (hh, ww, 1)), [0, 2], adam7=True)
+        yield "adam7_pal4_%dx%d" % (ww, hh), _png(ww, hh, 4, 3, rng.randint(0, 16, (hh, ww, 1)), [0, 1, 2], plte=pal, trns=rng.randint(0, 256, 5), adam7=True)
 
 
 CASES = list(_cases())

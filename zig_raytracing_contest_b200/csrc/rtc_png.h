@@ -4,7 +4,7 @@
 //                     produced in 1 MiB slices on all host threads).
 //   png_decode      : what stage1 asks of stb at src/stage1.zig:56-63 (stbi_loadf_from_memory(..., 4)), for
 //                     PNG inputs: 8-bit RGBA out + the file's own channel count (`actual_c`). 16-bit samples keep
-//                     their high byte (stb's 16 -> 8 conversion); palette + tRNS expand; Adam7 is not supported.
+//                     their high byte (stb's 16 -> 8 conversion); palette + tRNS expand; colour keys; Adam7 interlace.
 #pragma once
 #include <zlib.h>
 
@@ -280,7 +280,7 @@ inline DecodedImage png_decode(const uint8_t* data, size_t n)
         p += 12 + (size_t)len;
     }
     if (img.w == 0 || img.h == 0) throw std::runtime_error("PNG: missing IHDR");
-    if (interlace) throw std::runtime_error("PNG: Adam7-interlaced images are not supported");
+    if (interlace > 1) throw std::runtime_error("PNG: bad interlace method");
     int ch;
     switch (ctype) {
         case 0: ch = 1; break;
@@ -292,62 +292,82 @@ inline DecodedImage png_decode(const uint8_t* data, size_t n)
     }
     if (!(depth == 8 || depth == 16 || ((ctype == 0 || ctype == 3) && (depth == 1 || depth == 2 || depth == 4))))
         throw std::runtime_error("PNG: unsupported bit depth");
-    const size_t bpp_bits = (size_t)ch * depth, stride = (img.w * bpp_bits + 7) / 8, bpp = (bpp_bits + 7) / 8;
-    std::vector<uint8_t> raw((stride + 1) * img.h);
+    if ((uint64_t)img.w * img.h > ((uint64_t)1 << 30)) throw std::runtime_error("PNG: image too large");
+    const size_t bpp_bits = (size_t)ch * depth, bpp = (bpp_bits + 7) / 8;
+    // the sub-images: one for a plain file, the seven Adam7 passes otherwise (each filtered on its own)
+    struct Pass { uint32_t x0, y0, dx, dy, w, h; };
+    std::vector<Pass> passes;
+    if (!interlace) passes.push_back(Pass{ 0, 0, 1, 1, img.w, img.h });
+    else {
+        static const uint32_t xo[7] = { 0, 4, 0, 2, 0, 1, 0 }, yo[7] = { 0, 0, 4, 0, 2, 0, 1 }, xs[7] = { 8, 8, 4, 4, 2, 2, 1 }, ys[7] = { 8, 8, 8, 4, 4, 2, 2 };
+        for (int k = 0; k < 7; ++k) {
+            const uint32_t pw = (img.w - xo[k] + xs[k] - 1) / xs[k], ph = (img.h - yo[k] + ys[k] - 1) / ys[k];
+            if (img.w > xo[k] && img.h > yo[k] && pw && ph) passes.push_back(Pass{ xo[k], yo[k], xs[k], ys[k], pw, ph });
+        }
+    }
+    size_t raw_size = 0;
+    for (const Pass& ps : passes) raw_size += (((size_t)ps.w * bpp_bits + 7) / 8 + 1) * ps.h;
+    std::vector<uint8_t> raw(raw_size);
     uLongf rn = (uLongf)raw.size();
     if (uncompress(raw.data(), &rn, idat.data(), (uLong)idat.size()) != Z_OK || rn != raw.size())
         throw std::runtime_error("PNG: inflate failed");
-    // undo the per-row filters in place
-    std::vector<uint8_t> prev(stride, 0);
-    for (uint32_t y = 0; y < img.h; ++y) {
-        uint8_t* row = raw.data() + (size_t)y * (stride + 1);
-        const int f = row[0];
-        uint8_t* cur = row + 1;
-        for (size_t i = 0; i < stride; ++i) {
-            const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
-            int v = cur[i];
-            switch (f) {
-                case 0: break;
-                case 1: v += a; break;
-                case 2: v += b; break;
-                case 3: v += (a + b) >> 1; break;
-                case 4: v += paeth(a, b, c); break;
-                default: throw std::runtime_error("PNG: bad filter");
-            }
-            cur[i] = (uint8_t)v;
-        }
-        memcpy(prev.data(), cur, stride);
-    }
     img.rgba.resize((size_t)img.w * img.h * 4);
-    auto sample = [&](const uint8_t* cur, size_t idx) -> int {          // idx-th sample of the row, as 8 bits
-        if (depth == 8) return cur[idx];
-        if (depth == 16) return cur[2 * idx];
-        const int per = 8 / depth, shift = (per - 1 - (int)(idx % per)) * depth;
-        const int v = (cur[idx / per] >> shift) & ((1 << depth) - 1);
-        return ctype == 3 ? v : v * 255 / ((1 << depth) - 1);
-    };
     img.actual_c = ctype == 3 ? (trns.empty() ? 3 : 4) : ch + ((ctype == 0 || ctype == 2) && !trns.empty() ? 1 : 0);
-    for (uint32_t y = 0; y < img.h; ++y) {
-        const uint8_t* cur = raw.data() + (size_t)y * (stride + 1) + 1;
-        uint8_t* o = img.rgba.data() + (size_t)y * img.w * 4;
-        for (uint32_t x = 0; x < img.w; ++x, o += 4) {
-            if (ctype == 3) {
-                const size_t i = (size_t)sample(cur, x);
-                if (3 * i + 2 >= plte.size()) throw std::runtime_error("PNG: palette index out of range");
-                o[0] = plte[3 * i]; o[1] = plte[3 * i + 1]; o[2] = plte[3 * i + 2];
-                o[3] = i < trns.size() ? trns[i] : 255;
-            } else if (ch <= 2) {
-                const int g = sample(cur, (size_t)x * ch);
-                o[0] = o[1] = o[2] = (uint8_t)g;
-                o[3] = ch == 2 ? (uint8_t)sample(cur, (size_t)x * 2 + 1) : 255;
-                if (ch == 1 && trns.size() >= 2 && depth == 8 && g == trns[1]) o[3] = 0;
-            } else {
-                o[0] = (uint8_t)sample(cur, (size_t)x * ch); o[1] = (uint8_t)sample(cur, (size_t)x * ch + 1);
-                o[2] = (uint8_t)sample(cur, (size_t)x * ch + 2);
-                o[3] = ch == 4 ? (uint8_t)sample(cur, (size_t)x * 4 + 3) : 255;
-                if (ch == 3 && trns.size() >= 6 && depth == 8 && o[0] == trns[1] && o[1] == trns[3] && o[2] == trns[5]) o[3] = 0;
+    const int scale = depth < 8 ? 255 / ((1 << depth) - 1) : 1;          // stb's depth scale: 0xff, 0x55, 0x11
+    auto key16 = [&](size_t k) { return trns.size() >= 2 * k + 2 ? ((int)trns[2 * k] << 8) | trns[2 * k + 1] : -1; };
+    uint8_t* base = raw.data();
+    for (const Pass& ps : passes) {
+        const size_t stride = ((size_t)ps.w * bpp_bits + 7) / 8;
+        std::vector<uint8_t> prev(stride, 0);
+        for (uint32_t y = 0; y < ps.h; ++y) {
+            uint8_t* row = base + (size_t)y * (stride + 1);
+            const int f = row[0];
+            uint8_t* cur = row + 1;
+            for (size_t i = 0; i < stride; ++i) {                       // undo the row filter in place
+                const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+                int v = cur[i];
+                switch (f) {
+                    case 0: break;
+                    case 1: v += a; break;
+                    case 2: v += b; break;
+                    case 3: v += (a + b) >> 1; break;
+                    case 4: v += paeth(a, b, c); break;
+                    default: throw std::runtime_error("PNG: bad filter");
+                }
+                cur[i] = (uint8_t)v;
+            }
+            memcpy(prev.data(), cur, stride);
+            auto raw_sample = [&](size_t idx) -> int {                  // idx-th sample of the row at the file's depth
+                if (depth == 8) return cur[idx];
+                if (depth == 16) return ((int)cur[2 * idx] << 8) | cur[2 * idx + 1];
+                const int per = 8 / depth, shift = (per - 1 - (int)(idx % per)) * depth;
+                return (cur[idx / per] >> shift) & ((1 << depth) - 1);
+            };
+            auto to8 = [&](int v) -> uint8_t { return (uint8_t)(depth == 16 ? v >> 8 : v * scale); };
+            for (uint32_t x = 0; x < ps.w; ++x) {
+                uint8_t* o = img.rgba.data() + (((size_t)ps.y0 + (size_t)y * ps.dy) * img.w + ps.x0 + (size_t)x * ps.dx) * 4;
+                if (ctype == 3) {
+                    const size_t i = (size_t)raw_sample(x);
+                    if (3 * i + 2 >= plte.size()) throw std::runtime_error("PNG: palette index out of range");
+                    o[0] = plte[3 * i]; o[1] = plte[3 * i + 1]; o[2] = plte[3 * i + 2];
+                    o[3] = i < trns.size() ? trns[i] : 255;
+                } else if (ch <= 2) {
+                    const int g = raw_sample((size_t)x * ch);
+                    o[0] = o[1] = o[2] = to8(g);
+                    o[3] = ch == 2 ? to8(raw_sample((size_t)x * 2 + 1)) : 255;
+                    // colour key (tRNS of a grey image): compared at 16 bits, else on the low byte at the scaled 8-bit value
+                    if (ch == 1 && key16(0) >= 0 && (depth == 16 ? g == key16(0) : to8(g) == (uint8_t)((key16(0) & 255) * scale))) o[3] = 0;
+                } else {
+                    const int r = raw_sample((size_t)x * ch), g = raw_sample((size_t)x * ch + 1), b = raw_sample((size_t)x * ch + 2);
+                    o[0] = to8(r); o[1] = to8(g); o[2] = to8(b);
+                    o[3] = ch == 4 ? to8(raw_sample((size_t)x * 4 + 3)) : 255;
+                    if (ch == 3 && key16(2) >= 0 &&
+                        (depth == 16 ? (r == key16(0) && g == key16(1) && b == key16(2))
+                                     : (r == (key16(0) & 255) && g == (key16(1) & 255) && b == (key16(2) & 255)))) o[3] = 0;
+                }
             }
         }
+        base += (stride + 1) * ps.h;
     }
     return img;
 }
