@@ -289,8 +289,8 @@ typedef struct rtc_host_scene {
  * .gltf (+ external buffers / PNG images / data: URIs) or .glb file. camera_name NULL = the first
  * camera; width/height 0 = not given (size rules of src/stage1.zig:322-342). PNG textures are
  * linearised like stb's stbi_loadf (pow(c/255.0f, 2.2f) in double, alpha linear). PNG (all colour types and
- * depths, Adam7) and JPEG (baseline / progressive Huffman, 1 or 3 components) decode to the bytes stb produces;
- * other formats and CMYK JPEGs are RTC_ERR_UNSUPPORTED. */
+ * depths, Adam7) and JPEG (baseline / progressive Huffman; grey, YCbCr, RGB, CMYK / YCCK) decode to the bytes stb produces;
+ * other formats are RTC_ERR_UNSUPPORTED. */
 int  rtc_gltf_load(const char* path, const char* camera_name, uint32_t width, uint32_t height,
                    int num_threads, rtc_host_scene* out);
 void rtc_host_scene_free(rtc_host_scene* scene);

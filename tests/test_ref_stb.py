@@ -267,6 +267,13 @@ def _jpeg_cases():
         yield "restart_rows_progressive", enc(img, quality=75, subsampling=1, restart_marker_rows=1, progressive=True)
     except TypeError:
         pass
+    b = io.BytesIO()
+    cmyk = np.concatenate([img, 255 - img[:, :, :1] // 2], axis=2)
+    PIL.fromarray(cmyk, "CMYK").save(b, "JPEG", quality=80)
+    yield "cmyk", b.getvalue()
+    b = io.BytesIO()
+    PIL.fromarray(cmyk, "CMYK").save(b, "JPEG", quality=60, progressive=True, subsampling=2)
+    yield "cmyk_progressive", b.getvalue()
     try:
         import cv2
         bgr = np.ascontiguousarray(img[:, :, ::-1])
@@ -295,21 +302,19 @@ def test_jpeg_textures_equal_stbi_loadf(stb, tmp_path):
         assert m.transparency.texels.shape == (1, 1, 1), name             # JPEG has no alpha (actual_c 3 or 1)
 
 
-def test_unsupported_jpegs_are_reported(tmp_path):
+def test_broken_jpegs_are_reported(tmp_path):
     PIL = pytest.importorskip("PIL.Image")
     import io
-    from zig_raytracing_contest_b200 import abi
-    b = io.BytesIO()
-    PIL.fromarray(np.zeros((8, 8, 4), np.uint8), "CMYK").save(b, "JPEG")
-    open(str(tmp_path / "cmyk.png"), "wb").write(b.getvalue())
-    with pytest.raises(rtc.RtcError) as e:
-        rtc.HostSceneData(_scene_with_images(tmp_path, ["cmyk"]), height=8)
-    assert e.value.code == abi.RTC_ERR_UNSUPPORTED and "CMYK" in str(e.value)
     good = io.BytesIO()
     PIL.fromarray(np.full((16, 16, 3), 90, np.uint8), "RGB").save(good, "JPEG")
     open(str(tmp_path / "cut.png"), "wb").write(good.getvalue()[:40])               # cut inside the tables
     with pytest.raises(rtc.RtcError):
         rtc.HostSceneData(_scene_with_images(tmp_path, ["cut"]), height=8)
+    data = bytearray(good.getvalue())
+    data[data.index(b"\xff\xc0") + 1] = 0xC9                                       # SOF9: arithmetic coding
+    open(str(tmp_path / "arith.png"), "wb").write(bytes(data))
+    with pytest.raises(rtc.RtcError, match="arithmetic"):
+        rtc.HostSceneData(_scene_with_images(tmp_path, ["arith"]), height=8)
 
 
 def test_stb_compatible_writer_is_byte_identical(stb, tmp_path, monkeypatch):

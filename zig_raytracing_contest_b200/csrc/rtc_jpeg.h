@@ -10,8 +10,9 @@
 //                                                    column pass, +128 and rounding folded into the row pass)
 //   chroma upsampling                   :3448-3653  (h2, v2, h2v2 triangle filters centred as JFIF, else replication)
 //   YCbCr -> RGB                        :3655-3682  (20-bit fixed point, the Cb term of green truncated to 16 bits)
-// Supported: 8-bit, 1 or 3 components (YCbCr, or RGB when an Adobe APP14 marker says so and there is no JFIF
-// header). 4-component (CMYK / YCCK) and arithmetic-coded files are reported as unsupported.
+// Supported: 8-bit, 1, 3 or 4 components (YCbCr, or RGB when an Adobe APP14 marker says so and there is no JFIF
+// header; CMYK / YCCK by the Adobe transform flag). Arithmetic-coded, lossless and hierarchical files are reported
+// as unsupported (stb rejects them too).
 #pragma once
 #include "rtc_png.h"
 
@@ -344,8 +345,7 @@ struct Decoder {
         if (height == 0 || width == 0) bad("zero image size");
         if (width > (1 << 24) || height > (1 << 24)) bad("image too large");
         ncomp = get8();
-        if (ncomp == 4) bad("4-component (CMYK / YCCK) files are not supported");
-        if (ncomp != 1 && ncomp != 3) bad("bad component count");
+        if (ncomp != 1 && ncomp != 3 && ncomp != 4) bad("bad component count");
         if (len != 8 + 3 * ncomp) bad("bad SOF length");
         for (int i = 0; i < ncomp; ++i) {
             Component& c = comp[i];
@@ -566,7 +566,7 @@ inline DecodedImage jpeg_decode(const uint8_t* data, size_t n)
     const bool is_rgb = z.ncomp == 3 && (z.adobe_transform == 0 && !z.jfif);     // stb also honours an 'R','G','B' component-id triple
     bool rgb_ids = z.ncomp == 3 && z.comp[0].id == 'R' && z.comp[1].id == 'G' && z.comp[2].id == 'B';
     struct Res { int hs, vs, ystep, w_lores, ypos; const uint8_t* line0; const uint8_t* line1; std::vector<uint8_t> buf; };
-    Res res[3];
+    Res res[4];
     for (int k = 0; k < z.ncomp; ++k) {
         Res& r = res[k];
         r.hs = z.hmax / z.comp[k].h; r.vs = z.vmax / z.comp[k].v;
@@ -579,7 +579,7 @@ inline DecodedImage jpeg_decode(const uint8_t* data, size_t n)
     const int c_y = (int)(1.40200f * 4096.0f + 0.5f) << 8, c_g1 = -((int)(0.71414f * 4096.0f + 0.5f) << 8),
               c_g2 = -((int)(0.34414f * 4096.0f + 0.5f) << 8), c_b = (int)(1.77200f * 4096.0f + 0.5f) << 8;
     for (int j = 0; j < z.height; ++j) {
-        const uint8_t* row[3] = { nullptr, nullptr, nullptr };
+        const uint8_t* row[4] = { nullptr, nullptr, nullptr, nullptr };
         for (int k = 0; k < z.ncomp; ++k) {
             Res& r = res[k];
             const bool bot = r.ystep >= (r.vs >> 1);
@@ -591,17 +591,27 @@ inline DecodedImage jpeg_decode(const uint8_t* data, size_t n)
             }
         }
         uint8_t* out = img.rgba.data() + (size_t)j * img.w * 4;
+        auto ycc = [&](int i, uint8_t* o) {
+            const int yf = (row[0][i] << 20) + (1 << 19), cb = row[1][i] - 128, cr = row[2][i] - 128;
+            int r = yf + cr * c_y;
+            int g = yf + cr * c_g1 + (int)((uint32_t)(cb * c_g2) & 0xffff0000u);
+            int b = yf + cb * c_b;
+            r >>= 20; g >>= 20; b >>= 20;
+            o[0] = Decoder::clamp8(r); o[1] = Decoder::clamp8(g); o[2] = Decoder::clamp8(b);
+        };
+        auto mul8 = [](int x, int y) { const unsigned t = (unsigned)(x * y + 128); return (uint8_t)((t + (t >> 8)) >> 8); };   // stb_image.h:3724
         for (int i = 0; i < z.width; ++i, out += 4) {
             if (z.ncomp == 1) { out[0] = out[1] = out[2] = row[0][i]; }
-            else if (is_rgb || rgb_ids) { out[0] = row[0][i]; out[1] = row[1][i]; out[2] = row[2][i]; }
-            else {
-                const int yf = (row[0][i] << 20) + (1 << 19), cb = row[1][i] - 128, cr = row[2][i] - 128;
-                int r = yf + cr * c_y;
-                int g = yf + cr * c_g1 + (int)((uint32_t)(cb * c_g2) & 0xffff0000u);
-                int b = yf + cb * c_b;
-                r >>= 20; g >>= 20; b >>= 20;
-                out[0] = Decoder::clamp8(r); out[1] = Decoder::clamp8(g); out[2] = Decoder::clamp8(b);
+            else if (z.ncomp == 4) {                                   // stb_image.h:3974-3996: CMYK, YCCK, or YCbCr + an ignored plane
+                const int k = row[3][i];
+                if (z.adobe_transform == 0) { out[0] = mul8(row[0][i], k); out[1] = mul8(row[1][i], k); out[2] = mul8(row[2][i], k); }
+                else {
+                    ycc(i, out);
+                    if (z.adobe_transform == 2) { out[0] = mul8(255 - out[0], k); out[1] = mul8(255 - out[1], k); out[2] = mul8(255 - out[2], k); }
+                }
             }
+            else if (is_rgb || rgb_ids) { out[0] = row[0][i]; out[1] = row[1][i]; out[2] = row[2][i]; }
+            else ycc(i, out);
             out[3] = 255;
         }
     }
