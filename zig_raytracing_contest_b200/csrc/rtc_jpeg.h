@@ -146,8 +146,8 @@ struct Decoder {
         memset(d, 0, 64 * sizeof(int16_t));
         const int t = decode(dc);
         if (t > 15) bad("bad DC size");
-        c.dc_pred += extend(t);
-        d[0] = (int16_t)(c.dc_pred * q[0]);
+        c.dc_pred = (int)((uint32_t)c.dc_pred + (uint32_t)extend(t));          // wraps (corrupt files), never overflows
+        d[0] = (int16_t)((uint32_t)c.dc_pred * (uint32_t)q[0]);
         for (int k = 1; k < 64;) {
             const int rs = decode(ac), s = rs & 15, r = rs >> 4;
             if (s == 0) {
@@ -167,8 +167,8 @@ struct Decoder {
             memset(d, 0, 64 * sizeof(int16_t));
             const int t = decode(hdc[c.hd]);
             if (t > 15) bad("bad DC size");
-            c.dc_pred += extend(t);
-            d[0] = (int16_t)(c.dc_pred * (1 << succ_low));
+            c.dc_pred = (int)((uint32_t)c.dc_pred + (uint32_t)extend(t));
+            d[0] = (int16_t)((uint32_t)c.dc_pred << succ_low);
         } else if (getbit()) d[0] = (int16_t)(d[0] + (int16_t)(1 << succ_low));
     }
     void block_prog_ac(int16_t d[64], Component& c)
@@ -235,28 +235,32 @@ struct Decoder {
 
     // ---- 8x8 inverse DCT, stb_image.h:2427-2516 ----
     static int fx(double x) { return (int)(x * 4096 + 0.5); }
-    struct Row { int x0, x1, x2, x3, t0, t1, t2, t3; };
-    static Row idct1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7)
+    // I = int for the column pass (16-bit inputs cannot overflow it); the row pass runs on its results, which a
+    // corrupt file can drive beyond what 32-bit products hold, so it uses 64 bits (same values whenever stb's int
+    // arithmetic does not overflow, defined behaviour when it would).
+    template <class I> struct RowT { I x0, x1, x2, x3, t0, t1, t2, t3; };
+    template <class I>
+    static RowT<I> idct1d(I s0, I s1, I s2, I s3, I s4, I s5, I s6, I s7)
     {
         static const int k0541 = fx(0.5411961f), k1847 = fx(-1.847759065f), k0765 = fx(0.765366865f), k1175 = fx(1.175875602f),
                          k0298 = fx(0.298631336f), k2053 = fx(2.053119869f), k3072 = fx(3.072711026f), k1501 = fx(1.501321110f),
                          k0899 = fx(-0.899976223f), k2562 = fx(-2.562915447f), k1961 = fx(-1.961570560f), k0390 = fx(-0.390180644f);
-        Row r;
-        int p1 = (s2 + s6) * k0541;
-        int t2 = p1 + s6 * k1847, t3 = p1 + s2 * k0765;
-        int t0 = (s0 + s4) * 4096, t1 = (s0 - s4) * 4096;
+        RowT<I> r;
+        I p1 = (s2 + s6) * k0541;
+        I t2 = p1 + s6 * k1847, t3 = p1 + s2 * k0765;
+        I t0 = (s0 + s4) * 4096, t1 = (s0 - s4) * 4096;
         r.x0 = t0 + t3; r.x3 = t0 - t3; r.x1 = t1 + t2; r.x2 = t1 - t2;
         t0 = s7; t1 = s5; t2 = s3; t3 = s1;
-        int p3 = t0 + t2, p4 = t1 + t3;
+        I p3 = t0 + t2, p4 = t1 + t3;
         p1 = t0 + t3;
-        int p2 = t1 + t2;
-        const int p5 = (p3 + p4) * k1175;
+        I p2 = t1 + t2;
+        const I p5 = (p3 + p4) * k1175;
         t0 = t0 * k0298; t1 = t1 * k2053; t2 = t2 * k3072; t3 = t3 * k1501;
         p1 = p5 + p1 * k0899; p2 = p5 + p2 * k2562; p3 = p3 * k1961; p4 = p4 * k0390;
         r.t3 = t3 + p1 + p4; r.t2 = t2 + p2 + p3; r.t1 = t1 + p2 + p4; r.t0 = t0 + p1 + p3;
         return r;
     }
-    static uint8_t clamp8(int x) { return (uint8_t)(x < 0 ? 0 : (x > 255 ? 255 : x)); }
+    static uint8_t clamp8(long long x) { return (uint8_t)(x < 0 ? 0 : (x > 255 ? 255 : x)); }
     static void idct(uint8_t* out, int stride, const int16_t d[64])
     {
         int val[64];
@@ -267,7 +271,7 @@ struct Decoder {
                 const int dc = c[0] * 4;
                 v[0] = v[8] = v[16] = v[24] = v[32] = v[40] = v[48] = v[56] = dc;
             } else {
-                Row r = idct1d(c[0], c[8], c[16], c[24], c[32], c[40], c[48], c[56]);
+                RowT<int> r = idct1d<int>(c[0], c[8], c[16], c[24], c[32], c[40], c[48], c[56]);
                 r.x0 += 512; r.x1 += 512; r.x2 += 512; r.x3 += 512;
                 v[0] = (r.x0 + r.t3) >> 10; v[56] = (r.x0 - r.t3) >> 10;
                 v[8] = (r.x1 + r.t2) >> 10; v[48] = (r.x1 - r.t2) >> 10;
@@ -278,8 +282,8 @@ struct Decoder {
         for (int i = 0; i < 8; ++i) {
             const int* v = val + 8 * i;
             uint8_t* o = out + (size_t)i * stride;
-            Row r = idct1d(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
-            const int bias = 65536 + (128 << 17);
+            RowT<long long> r = idct1d<long long>(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+            const long long bias = 65536 + (128 << 17);
             r.x0 += bias; r.x1 += bias; r.x2 += bias; r.x3 += bias;
             o[0] = clamp8((r.x0 + r.t3) >> 17); o[7] = clamp8((r.x0 - r.t3) >> 17);
             o[1] = clamp8((r.x1 + r.t2) >> 17); o[6] = clamp8((r.x1 - r.t2) >> 17);
