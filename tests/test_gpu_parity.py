@@ -184,3 +184,68 @@ def test_edge_cases(orc):
     o = orc.render(scene.desc, cams[0], rtc.make_params(num_samples=4, seed=1), want_radiance=True)
     assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"])) and g["stats"]["hits_shaded"] == 0
     scene.close()
+
+
+@pytest.mark.parametrize("seed,res", [(0, (8, 8, 8)), (1, (12, 4, 20)), (2, (7, 5, 3)), (3, (16, 16, 4)), (4, (1, 9, 2)), (5, (32, 32, 32))])
+def test_random_soups_with_exact_ties(orc, seed, res):
+    """Random triangle soups built to provoke what procedural scenes avoid: exact duplicates and coplanar overlapping
+    triangles (equal t: the first tested must win — cell order, then source order), triangles spanning the whole grid,
+    slivers, zero-area triangles, axis-aligned quads on integer coordinates seen by rays through their shared edges,
+    grids that are and are not multiples of the 4x4x4 block (two-level walk on / off), cameras inside and outside.
+    Hit ids, t/u/v, radiance and the traversal counters against the oracle, for the uploaded and the device-built scene."""
+    rng = np.random.RandomState(100 + seed)
+    tris = []
+    c = rng.uniform(-1, 1, (60, 1, 3))
+    tris.append(c + rng.normal(0, 0.25, (60, 3, 3)))                                   # ordinary
+    tris.append(rng.uniform(-1.2, 1.2, (6, 3, 3)))                                     # spanning many cells
+    base = c[:8] + rng.normal(0, 0.3, (8, 3, 3))
+    tris += [base, base.copy(), base[:, [1, 2, 0]]]                                    # duplicates (and a rotated vertex order)
+    q = np.array([[[0, 0, 0], [1, 0, 0], [1, 1, 0]], [[0, 0, 0], [1, 1, 0], [0, 1, 0]]], np.float64)
+    for ox in (-1, 0):
+        for oy in (-1, 0):
+            tris.append(q + (ox, oy, -0.5))                                            # a 2x2 wall of unit quads at z = -0.5
+    tris.append(q * 1.5 + (-0.75, -0.75, -0.5))                                        # coplanar with the wall, overlapping it
+    p = rng.uniform(-1, 1, (5, 1, 3))
+    tris.append(np.concatenate([p, p, p + rng.normal(0, 0.2, (5, 1, 3))], axis=1))     # zero area
+    tris.append(np.concatenate([p, p + 1e-4, p + rng.normal(0, 0.5, (5, 1, 3))], axis=1))   # slivers
+    pos = np.concatenate(tris).astype(np.float32)
+    n = len(pos)
+    td = np.zeros(n, rtc.TRI_DATA_DTYPE)
+    e1, e2 = pos[:, 1] - pos[:, 0], pos[:, 2] - pos[:, 0]
+    nrm = np.cross(e1, e2)
+    ln = np.linalg.norm(nrm, axis=1, keepdims=True)
+    nrm = np.where(ln > 0, nrm / np.maximum(ln, 1e-30), (0, 0, 1)).astype(np.float32)
+    td["normal"][:] = nrm[:, None, :]
+    td["texcoord"][:] = rng.uniform(0, 1, (n, 3, 2))
+    td["material"][:] = rng.randint(0, 3, n)
+    M = rtc.MaterialData
+    mats = [M(base_color=(0.7, 0.6, 0.5)), M(base_color=(0.2, 0.5, 0.8), emissive=(1.5, 1.2, 0.9)),
+            M(base_color=rtc.TextureData(rng.uniform(0, 1, (8, 8, 3)).astype(np.float32)),
+              transparency=rtc.TextureData((rng.uniform(0, 1, (4, 4, 1)) > 0.4).astype(np.float32)))]
+    geo = rtc.Geometry(pos, td, res)
+    a = rtc.Scene(geo, mats, device=0)
+    b = rtc.Scene.from_soup(pos, td, res, mats, device=0)
+    ogeo = orc.Geometry(pos, td, res)
+    assert np.array_equal(geo.cells, ogeo.cells) and np.array_equal(geo.tri_data["src_tri"], ogeo.indices.astype(np.uint32))
+    cams = [scenes.load_camera(scenes.look_at((0.0, 0.0, 3.0), (0, 0, -0.5)), 0.9, 1.0, None, 64),     # pixel centres meet the wall's edges
+            scenes.load_camera(scenes.look_at((0.3, -0.2, 0.1), (1, 0.5, -1)), 1.2, 1.5, None, 48),    # inside the soup
+            scenes.load_camera(scenes.look_at((2.5, 2.0, -2.0), (0, 0, 0)), 0.7, 1.0, None, 48)]
+    for cam in cams:
+        for prm in (rtc.make_params(mode=abi.RTC_MODE_PRIMARY), rtc.make_params(num_samples=3, max_bounce=4, seed=seed)):
+            o = orc.render(a.desc, cam, prm, want_radiance=True, want_hits=True, want_stats=True)
+            primary = prm.mode == abi.RTC_MODE_PRIMARY
+            for scene in (a, b):
+                g = scene.render(cam, prm, want_radiance=True, want_hits=True, want_stats=True)
+                if primary:
+                    assert np.array_equal(g["hit_id"], o["hit_id"])
+                    assert np.array_equal(_bits(g["hit_tuv"]), _bits(o["hit_tuv"]))
+                assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"]))
+                for k in ("rays", "cells_visited", "tris_tested", "hits_shaded", "paths"):
+                    assert g["stats"][k] == o["stats"][k], k
+            # the production kernels (no counters: two-level walk where the grid allows it) give the same frame
+            g = a.render(cam, prm, want_radiance=True, want_hits=True)
+            assert np.array_equal(_bits(g["radiance"]), _bits(o["radiance"]))
+            if primary:
+                assert np.array_equal(g["hit_id"], o["hit_id"])
+                assert (o["hit_id"] != 0xFFFFFFFF).sum() > 100
+    a.close(); b.close()
