@@ -342,3 +342,30 @@ def test_stb_compatible_writer_is_byte_identical(stb, tmp_path, monkeypatch):
         a, b = open(mine, "rb").read(), open(theirs, "rb").read()
         assert a == b, (k, img.shape, len(a), len(b))
         assert np.array_equal(rtc.png_read(mine), img)
+
+
+def test_committed_stb_vectors(tmp_path, monkeypatch):
+    """tests/golden/stb_golden.npz holds outputs of the reference's own unit (made by tests/golden/make_stb_golden.py where
+    /root/reference exists): stbi_loadf_from_memory(..., 4) of 20 small PNG / JPEG files and the files stbi_write_png
+    wrote for 3 frames. Checked on every machine, with or without the built unit."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "stb_golden.npz"))
+    names = [str(n) for n in g["names"]]
+    assert len(names) >= 20
+    for n in names:
+        open(str(tmp_path / (n + ".png")), "wb").write(g["file_" + n].tobytes())
+    hs = rtc.HostSceneData(_scene_with_images(tmp_path, names), height=8, num_threads=2)
+    for i, n in enumerate(names):
+        want, m = g["loadf_" + n], hs.materials[i]
+        assert np.array_equal(m.base_color.texels.view(np.uint32), np.ascontiguousarray(want[:, :, :3]).view(np.uint32)), n
+        if int(g["comp_" + n]) in (2, 4):
+            assert np.array_equal(m.transparency.texels[:, :, 0].view(np.uint32), np.ascontiguousarray(want[:, :, 3]).view(np.uint32)), n
+        else:
+            assert m.transparency.texels.shape == (1, 1, 1), n
+    monkeypatch.setenv("RTC_PNG_STB", "1")
+    for f in [str(x) for x in g["frames"]]:
+        path = str(tmp_path / (f + "_out.png"))
+        rtc.png_write(path, g["frame_" + f])
+        assert open(path, "rb").read() == g["png_" + f].tobytes(), f
+        theirs = str(tmp_path / (f + "_stb.png"))
+        open(theirs, "wb").write(g["png_" + f].tobytes())
+        assert np.array_equal(rtc.png_read(theirs), g["frame_" + f]), f
