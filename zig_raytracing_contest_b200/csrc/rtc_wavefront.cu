@@ -490,7 +490,26 @@ static void run_trace(const DevScene& sc, const WaveScratch& ws, uint32_t bounce
     const size_t smem = CSM ? sc.coarse_words * sizeof(uint32_t) : 0;
     static int per_sm[2] = { 0, 0 };                 // occupancy query cached per coarse-bitmap size class
     static size_t per_sm_smem[2] = { ~(size_t)0, ~(size_t)0 };
-    if (per_sm_smem[STATS] != smem) { per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); per_sm_smem[STATS] = smem; }
+    if (per_sm_smem[STATS] != smem) {
+        per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); per_sm_smem[STATS] = smem;
+        // Ask for no more shared memory than the resident CTAs use (static + coarse bitmap + 1 KiB the system reserves
+        // per CTA), so that the rest of the 256 KiB stays L1: the triangle and cell gathers are what the kernel waits
+        // on. +1.2 % on the 5 M-triangle scene, +0.9 % on the atrium; a carveout below the need costs occupancy (-14 %),
+        // hence the margin. RTC_CARVEOUT=<percent> overrides.
+        cudaFuncAttributes fa;
+        cudaDeviceProp prop;
+        int dev = 0;
+        int pct = -1;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&prop, dev) == cudaSuccess &&
+            cudaFuncGetAttributes(&fa, kern) == cudaSuccess && prop.sharedMemPerMultiprocessor > 0) {
+            const double need = (double)per_sm[STATS] * ((double)fa.sharedSizeBytes + (double)smem + 1024.0);
+            pct = (int)(100.0 * need / (double)prop.sharedMemPerMultiprocessor) + 3;
+            if (pct > 100) pct = 100;
+        }
+        if (const char* env = getenv("RTC_CARVEOUT")) pct = atoi(env);
+        if (pct >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaGetLastError();
+    }
     TraceTimer* tm = cfg.timer;
     const bool timed = tm && tm->used < tm->capacity;
     if (tm && !timed) tm->dropped += 1;
