@@ -50,6 +50,7 @@ def build_workload(name):
     scene_name, kw, grid, height, spp, bounce = WORKLOADS[name]
     spp = OVERRIDE.get("spp") or spp
     height = OVERRIDE.get("height") or height
+    grid = OVERRIDE.get("grid") or grid
     spec = scenes.SCENES[scene_name](**kw)
     t0 = time.time()
     geo = rtc.Geometry(spec.positions, spec.tri_data, grid)
@@ -155,8 +156,8 @@ def run_reference(args, rank, world):
 
 
 def workload_config(name, spec, geo, cam, spp, bounce, world, tiles=0):
-    if OVERRIDE.get("spp") or OVERRIDE.get("height"):
-        name = "%s [override spp=%s height=%s]" % (name, OVERRIDE.get("spp") or "-", OVERRIDE.get("height") or "-")
+    if OVERRIDE.get("spp") or OVERRIDE.get("height") or OVERRIDE.get("grid"):
+        name = "%s [override spp=%s height=%s grid=%s]" % (name, OVERRIDE.get("spp") or "-", OVERRIDE.get("height") or "-", OVERRIDE.get("grid") or "-")
     sharding = "none"
     if world > 1:
         sharding = ("strips of %d rows dealt round-robin, scene replicated, one NCCL gather of the RGB8 strips" % tiles) if tiles \
@@ -195,15 +196,17 @@ def run_gpu(args, rank, world, local_rank):
                         "note": "rtc_scene_create_from_soup, second call: grid-build kernels (CUDA events) / whole call incl. H2D of the soup and textures"}
     P = cam.w * cam.h
     math = abi.RTC_MATH_FAST if args.math == "fast" else abi.RTC_MATH_EXACT
+    accel = abi.RTC_ACCEL_BVH if args.accel == "bvh" else abi.RTC_ACCEL_GRID
+    bvh_info = scene.build_bvh() if accel == abi.RTC_ACCEL_BVH else None
     tiles = args.tile_rows if (args.sharding == "tiles" and world > 1) else 0
     if tiles:
         total = spp                                 # strong scaling: the frame is fixed, its pixels are dealt over the ranks
-        prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, total_samples=total, math=math,
+        prm = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, total_samples=total, math=math, accel=accel,
                               tile_rank=rank, tile_world=world, tile_rows=tiles)
     else:
         total = spp * world                         # weak scaling: the frame's sample count grows with N
         s_off, s_cnt = shard.sample_shard(rank, world, total)
-        prm = rtc.make_params(num_samples=s_cnt, max_bounce=bounce, seed=SEED, sample_offset=s_off, total_samples=total, math=math)
+        prm = rtc.make_params(num_samples=s_cnt, max_bounce=bounce, seed=SEED, sample_offset=s_off, total_samples=total, math=math, accel=accel)
     acc = torch.zeros(P, 4, device=dev)
     d_rgb = torch.zeros(P * 3, dtype=torch.uint8, device=dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
@@ -288,14 +291,17 @@ def run_gpu(args, rank, world, local_rank):
     if rank == 0:
         # instrumented launch of the same frame: counts behind the algorithmic bytes
         prm_s = rtc.make_params(num_samples=spp, max_bounce=bounce, seed=SEED, sample_offset=0, total_samples=total,
-                                math=math, collect_stats=True, tile_rank=rank if tiles else 0, tile_world=world if tiles else 0,
+                                math=math, accel=accel, collect_stats=True, tile_rank=rank if tiles else 0, tile_world=world if tiles else 0,
                                 tile_rows=tiles)
         acc.zero_(); torch.cuda.synchronize()
         scene.stats()
         scene.render_accumulate(cam, prm_s, acc.data_ptr(), stream)
         cs = scene.stats()
         algo_bytes = rtc.bytes_per_frame(cs, P)
-        trav_bytes = 8 * cs["cells_visited"] + 48 * cs["tris_tested"]      # k_trace's share: Cell + {v0,e1,e2} records
+        rec = 80 if bvh_info else 8                                         # BVH: 80-byte nodes; grid: 8-byte Cell records
+        trav_bytes = rec * cs["cells_visited"] + 48 * cs["tris_tested"]    # k_trace's share: Cell / node + {v0,e1,e2} records
+        if bvh_info:
+            algo_bytes += (80 - 8) * cs["cells_visited"]
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -307,7 +313,10 @@ def run_gpu(args, rank, world, local_rank):
         cfg["math"] = "exact (no FMA contraction)" if math == abi.RTC_MATH_EXACT else "fast (FMA contraction)"
         cfg["host_build_s"] = round(build_s, 3); cfg["scene_upload_s"] = round(upload_s, 3)
         cfg["device_build"] = device_build
-        cfg["per_ray"] = {"cells": round(cs["cells_visited"] / cs["rays"], 2), "tris": round(cs["tris_tested"] / cs["rays"], 2),
+        cfg["accel"] = "bvh8 (RTC_ACCEL_BVH, opt-in)" if bvh_info else "grid (the reference's structure)"
+        if bvh_info:
+            cfg["bvh"] = bvh_info
+        cfg["per_ray"] = {"nodes" if bvh_info else "cells": round(cs["cells_visited"] / cs["rays"], 2), "tris": round(cs["tris_tested"] / cs["rays"], 2),
                           "bytes": round(algo_bytes / cs["rays"], 1), "rays_per_path": round(cs["rays"] / cs["paths"], 3)}
         out = {
             "metric": "Mrays/s", "value": round(value, 2), "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
@@ -319,7 +328,7 @@ def run_gpu(args, rank, world, local_rank):
             "gpu_launches": launches,
             "kernel_ms": {"render_kernels_per_step": round(kern_ms, 3), "k_trace_per_step": round(trace_ms, 3),
                           "k_trace_share": round(trace_ms / max(kern_ms, 1e-9), 4)},
-            "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "k_trace_bvh" if bvh_info else "k_trace", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 5), "traffic": TRAFFIC.get(args.workload),
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "launches_per_step": round(trace_launches, 1),
@@ -370,6 +379,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--accel", default="grid", choices=["grid", "bvh"],
+                    help="grid: the reference's structure, bit-exact (default); bvh: RTC_ACCEL_BVH (same triangle test, enumerated near-ties)")
     ap.add_argument("--sharding", default="samples", choices=["samples", "tiles"],
                     help="N > 1: sample ranges + reduce (weak scaling, default) or row strips + gather (strong scaling, cfg4)")
     ap.add_argument("--tile-rows", type=int, default=8, help="--sharding tiles: rows per strip")
@@ -378,8 +389,10 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=0, help="--impl reference: rows per step (0 = calibrate to ~8 s)")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (profiling only)")
     ap.add_argument("--height", type=int, default=0, help="override the workload's height (profiling only)")
+    ap.add_argument("--grid", type=int, nargs=3, default=None,
+                    help="override grid_resolution (a config.json key of the reference, src/main.zig:56-61)")
     args = ap.parse_args()
-    OVERRIDE.update(spp=args.spp, height=args.height)
+    OVERRIDE.update(spp=args.spp, height=args.height, grid=tuple(args.grid) if args.grid else None)
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 6u
+#define RTC_ABI_VERSION 7u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -124,9 +124,17 @@ enum {
                               hit -> emissive, miss -> sky; fills rtc_aux hit buffers */
 };
 
-/* Traversal selector (results are identical except in exact-t ties). */
+/* Traversal selector. Both run the reference's Triangle.rayIntersection (src/linalg.zig:696-722)
+ * with identical arithmetic, so t, u, v of a hit are the same bits whichever structure found the triangle.
+ *   GRID: the reference's structure and visiting order — results bit-identical to the oracle. The default.
+ *   BVH : opt-in 8-wide BVH with quantised 80-byte nodes over the source triangles (no duplication). Same nearest hit
+ *         except (a) exact-t ties between two triangles go to the smaller source id instead of the grid's
+ *         first-visited, (b) hits the grid's binning / crossing arithmetic loses or finds at the edge of a cell.
+ *         tests/test_gpu_bvh.py enumerates both against the oracle ("bit-exact except enumerated
+ *         near-ties"). Built on first use, or ahead of time with rtc_scene_build_bvh. */
 enum {
-    RTC_ACCEL_GRID = 0     /* uniform grid + 3D-DDA in the reference's cell order; resolution <= 1024 per axis */
+    RTC_ACCEL_GRID = 0,    /* uniform grid + 3D-DDA in the reference's cell order; resolution <= 1024 per axis */
+    RTC_ACCEL_BVH = 1
 };
 
 /* Arithmetic contract. EXACT: no FMA contraction anywhere the reference has separate
@@ -158,7 +166,7 @@ typedef struct rtc_params {
 /* Counters behind SURVEY §8(d)'s bytes-per-ray figure. */
 typedef struct rtc_stats {
     uint64_t rays;           /* traceRay invocations (camera + bounce + alpha continuation) */
-    uint64_t cells_visited;  /* 8-byte Cell records fetched                                  */
+    uint64_t cells_visited;  /* 8-byte Cell records fetched (RTC_ACCEL_BVH: 80-byte nodes)   */
     uint64_t tris_tested;    /* 48-byte {v0,e1,e2} records fetched                           */
     uint64_t hits_shaded;    /* hits that fetched triangle data + 3 textures                 */
     uint64_t paths;          /* camera rays                                                  */
@@ -208,6 +216,18 @@ int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples
 /* Fetches and clears the ray/traversal counters accumulated on the scene's device
  * since the last call (synchronises the device). */
 int rtc_scene_stats(rtc_scene* scene, rtc_stats* out);
+
+/* RTC_ACCEL_BVH's structure: built on the host threads (num_threads < 1 = all) from the scene's own device-resident
+ * {v0,e1,e2} records — whichever way the scene came to exist — and uploaded next to the grid. Idempotent. */
+typedef struct rtc_bvh_info {
+    uint32_t num_nodes;      /* 80-byte nodes                                   */
+    uint32_t num_tris;       /* triangles referenced (each source triangle once) */
+    uint32_t depth;          /* levels of inner nodes                            */
+    uint32_t reserved;
+    uint64_t bytes;          /* device bytes of nodes + triangle records         */
+    double   build_ms;       /* wall time of download + build + upload           */
+} rtc_bvh_info;
+int rtc_scene_build_bvh(rtc_scene* scene, int num_threads, rtc_bvh_info* info /* may be NULL */);
 
 /* ---- stage2 as the path's producer ------------------------------ */
 

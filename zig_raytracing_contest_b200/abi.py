@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 6
+RTC_ABI_VERSION = 7
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -19,6 +19,7 @@ RTC_ERR_UNSUPPORTED = 7
 RTC_MODE_PATH = 0
 RTC_MODE_PRIMARY = 1
 RTC_ACCEL_GRID = 0
+RTC_ACCEL_BVH = 1
 RTC_MATH_EXACT = 0
 RTC_MATH_FAST = 1
 
@@ -98,6 +99,11 @@ class Aux(C.Structure):           # rtc_aux
                 ("radiance", C.POINTER(C.c_float)), ("stats", C.POINTER(Stats))]
 
 
+class BvhInfo(C.Structure):       # rtc_bvh_info
+    _fields_ = [("num_nodes", C.c_uint32), ("num_tris", C.c_uint32), ("depth", C.c_uint32), ("reserved", C.c_uint32),
+                ("bytes", C.c_uint64), ("build_ms", C.c_double)]
+
+
 class Geometry(C.Structure):      # rtc_geometry
     _fields_ = [("grid", Grid),
                 ("cells", C.POINTER(Cell)), ("num_cells", C.c_uint64),
@@ -130,7 +136,7 @@ class HostScene(C.Structure):     # rtc_host_scene
 # Every symbol include/rtc.h declares (checked by tests/test_abi.py against the built library).
 EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
-    "rtc_resolve", "rtc_scene_stats", "rtc_geometry_build", "rtc_geometry_free",
+    "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_geometry_build_device", "rtc_scene_create_from_soup",
     "rtc_scene_create_from_gltf", "rtc_gltf_load_device",
     "rtc_last_error", "rtc_abi_version", "rtc_device_count",

@@ -2,7 +2,9 @@
 // Replaces `scene.render(threads, camera, img)` (src/main.zig:126, src/stage3.zig:247).
 // No CPU fallback: every compute entry point fails with RTC_ERR_NO_DEVICE without an sm_100 GPU.
 #include "rtc_internal.h"
+#include "rtc_bvh_host.h"
 
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -228,6 +230,7 @@ int rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uin
 
 int rtc_scene_finish_(rtc_scene* s)
 {
+    s->dev.tri_mul = 1u;
     if (int rc = s->alloc(&s->counters, (size_t)rtc::CNT_N)) return rc;
     if (int rc = s->alloc(&s->work, (size_t)4)) return rc;
     CU(cudaMemset(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long)));
@@ -316,7 +319,7 @@ int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_param
     if (cam->w == 0 || cam->h == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "camera has zero size");
     if ((uint64_t)cam->w * cam->h >= ((uint64_t)1 << 31)) return fail(RTC_ERR_UNSUPPORTED, "more than 2^31 pixels");
     if (p->mode != RTC_MODE_PATH && p->mode != RTC_MODE_PRIMARY) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown mode %u", p->mode);
-    if (p->accel != RTC_ACCEL_GRID) return fail(RTC_ERR_UNSUPPORTED, "unknown accel %u", p->accel);
+    if (p->accel != RTC_ACCEL_GRID && p->accel != RTC_ACCEL_BVH) return fail(RTC_ERR_UNSUPPORTED, "unknown accel %u", p->accel);
     if (p->math != RTC_MATH_EXACT && p->math != RTC_MATH_FAST) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown math contract %u", p->math);
     if (p->mode == RTC_MODE_PATH && p->max_bounce > rtc::kMaxBounce)
         return fail(RTC_ERR_UNSUPPORTED, "max_bounce %u > %u (per-bounce queue bookkeeping of the kernels)", (unsigned)p->max_bounce, rtc::kMaxBounce);
@@ -426,10 +429,19 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
     const rtc::DevCamera dc = to_dev(*cam);
     rtc::LaunchCfg cfg; cfg.sm_count = s->sm_count; cfg.stream = stream; cfg.stats = p->collect_stats != 0;
     cfg.timer = &s->timer;
+    cfg.cache = &s->cache;
     uint32_t launches = 0;
+    const rtc::BvhView* bvh = nullptr;
+    rtc::DevScene dev = s->dev;
+    if (p->accel == RTC_ACCEL_BVH) {
+        if (!s->has_bvh) { if (int rc = rtc_scene_build_bvh(s, 0, nullptr)) return rc; }
+        bvh = &s->bvh;
+        // the shading kernel fetches the hit triangle through these: one {v0,e1,e2} record per BVH triangle
+        dev.tri_v0 = s->bvh.tris; dev.tri_e1 = s->bvh.tris + 1; dev.tri_e2 = s->bvh.tris + 2; dev.tri_mul = 3u;
+    }
     const cudaError_t e = p->math == RTC_MATH_FAST
-        ? rtc::fast::launch_render(s->dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches)
-        : rtc::exact::launch_render(s->dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches);
+        ? rtc::fast::launch_render(dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches, bvh)
+        : rtc::exact::launch_render(dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches, bvh);
     s->launches += launches;
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     return RTC_OK;
@@ -573,6 +585,63 @@ int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples
     cudaError_t e = rtc::exact::launch_resolve((const float4*)d_accum, num_pixels, total_samples, (uint8_t*)d_rgb,
                                                (float*)d_radiance, (cudaStream_t)stream);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
+    return RTC_OK;
+}
+
+int rtc_scene_build_bvh(rtc_scene* s, int num_threads, rtc_bvh_info* info)
+{
+    if (!s) return fail(RTC_ERR_INVALID_ARGUMENT, "null scene");
+    if (s->has_bvh) { if (info) *info = s->bvh_info; return RTC_OK; }
+    DeviceGuard guard(s->device);
+    const auto t0 = std::chrono::steady_clock::now();
+    // the scene's own records, whichever way it was created: baked (duplicated, cell-ordered) {v0 | src} {e1} {e2};
+    // every source triangle is taken once, from its first baked copy
+    const size_t M = (size_t)s->num_tris;
+    std::vector<float4> v0(M), e1(M), e2(M);
+    if (M) {
+        CU(cudaMemcpy(v0.data(), s->dev.tri_v0, M * sizeof(float4), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(e1.data(), s->dev.tri_e1, M * sizeof(float4), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(e2.data(), s->dev.tri_e2, M * sizeof(float4), cudaMemcpyDeviceToHost));
+    }
+    std::vector<uint32_t> first(s->num_src_tris, 0xFFFFFFFFu);
+    std::vector<uint32_t> uniq;
+    uniq.reserve(s->num_src_tris);
+    for (size_t i = 0; i < M; ++i) {
+        uint32_t src; memcpy(&src, &v0[i].w, sizeof src);
+        if (src >= s->num_src_tris) return fail(RTC_ERR_INVALID_ARGUMENT, "baked triangle %zu has source id %u of %u", i, src, s->num_src_tris);
+        if (first[src] == 0xFFFFFFFFu) { first[src] = (uint32_t)i; uniq.push_back((uint32_t)i); }
+    }
+    const uint32_t N = (uint32_t)uniq.size();
+    std::vector<float> rec((size_t)N * 12);
+    for (uint32_t k = 0; k < N; ++k) {
+        const uint32_t i = uniq[k];
+        float* r = &rec[12 * (size_t)k];
+        r[0] = v0[i].x; r[1] = v0[i].y; r[2] = v0[i].z; r[3] = v0[i].w;
+        r[4] = e1[i].x; r[5] = e1[i].y; r[6] = e1[i].z; r[7] = 0.0f;
+        r[8] = e2[i].x; r[9] = e2[i].y; r[10] = e2[i].z; r[11] = 0.0f;
+    }
+    RtcBvhHost h;
+    const int brc = rtc_bvh_build_host(rec.data(), N, num_threads, h);
+    if (brc != 0) return fail(RTC_ERR_UNSUPPORTED, "BVH build failed (code %d): coordinates outside the quantisation range or a leaf overflow", brc);
+    if (h.depth + 1 >= rtc::kBvhStack) return fail(RTC_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack (%u)", h.depth, rtc::kBvhStack);
+    std::vector<float4> bt(3 * (size_t)N + 3, make_float4(0, 0, 0, 0));
+    for (uint32_t k = 0; k < N; ++k) {
+        const float* r = &rec[12 * (size_t)h.order[k]];
+        bt[3 * (size_t)k] = make_float4(r[0], r[1], r[2], r[3]);
+        bt[3 * (size_t)k + 1] = make_float4(r[4], r[5], r[6], 0.0f);
+        bt[3 * (size_t)k + 2] = make_float4(r[8], r[9], r[10], 0.0f);
+    }
+    float4* d_nodes = nullptr; float4* d_tris = nullptr;
+    if (int rc = s->alloc(&d_nodes, 5 * (size_t)h.num_nodes)) return rc;
+    if (int rc = s->alloc(&d_tris, bt.size())) return rc;
+    CU(cudaMemcpy(d_nodes, h.nodes.data(), 80 * (size_t)h.num_nodes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_tris, bt.data(), bt.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    s->bvh.nodes = d_nodes; s->bvh.tris = d_tris;
+    s->bvh_info.num_nodes = h.num_nodes; s->bvh_info.num_tris = N; s->bvh_info.depth = h.depth; s->bvh_info.reserved = 0;
+    s->bvh_info.bytes = 80ull * h.num_nodes + 48ull * N;
+    s->bvh_info.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    s->has_bvh = true;
+    if (info) *info = s->bvh_info;
     return RTC_OK;
 }
 

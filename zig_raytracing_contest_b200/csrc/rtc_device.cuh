@@ -48,6 +48,7 @@ struct DevScene {
     uint32_t shift[3];          // bit position of the block coordinate of x, y, z (6, 6+lx, 6+lx+ly)
     uint32_t coarse_words;
     uint32_t num_materials;
+    uint32_t tri_mul;           // index step of tri_v0/e1/e2: 1 = three SoA arrays (grid), 3 = one {v0,e1,e2} record per triangle (BVH)
 };
 static constexpr uint32_t kMaxGridRes = 1024;     // packed cell: 6 + 3*8 bits
 static constexpr uint32_t kCoarseSmemMaxWords = 8192;   // 32 KiB: the coarse bitmap of a 256^3 grid
@@ -112,28 +113,28 @@ enum { CNT_RAYS = 0, CNT_CELLS = 1, CNT_TRIS = 2, CNT_HITS = 3, CNT_PATHS = 4, C
 
 // ---- Vec3 (src/linalg.zig:13-222) -----------------------------------------------------
 struct v3 { float x, y, z; };
-__device__ __forceinline__ v3 mk(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ v3 splat(float s) { return mk(s, s, s); }
-__device__ __forceinline__ v3 from(const float* a) { return mk(a[0], a[1], a[2]); }
-__device__ __forceinline__ v3 operator+(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ v3 operator-(v3 a, v3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ v3 operator*(v3 a, v3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ v3 operator/(v3 a, v3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }
-__device__ __forceinline__ v3 scale(v3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ __forceinline__ v3 mk(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
+__host__ __device__ __forceinline__ v3 splat(float s) { return mk(s, s, s); }
+__host__ __device__ __forceinline__ v3 from(const float* a) { return mk(a[0], a[1], a[2]); }
+__host__ __device__ __forceinline__ v3 operator+(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ __forceinline__ v3 operator-(v3 a, v3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ __forceinline__ v3 operator*(v3 a, v3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__host__ __device__ __forceinline__ v3 operator/(v3 a, v3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }
+__host__ __device__ __forceinline__ v3 scale(v3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
 // linalg.zig:189-191 — @reduce(.Add) keeps lane order: (x + y) + z
-__device__ __forceinline__ float dot(v3 a, v3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__host__ __device__ __forceinline__ float dot(v3 a, v3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 // linalg.zig:172-179 — a.yzx*b.zxy - a.zxy*b.yzx
-__device__ __forceinline__ v3 cross(v3 a, v3 b)
+__host__ __device__ __forceinline__ v3 cross(v3 a, v3 b)
 {
     return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 // linalg.zig:119-125 — normalize = scale(1.0 / length)
-__device__ __forceinline__ float length(v3 a) { return sqrtf(dot(a, a)); }
-__device__ __forceinline__ v3 normalize(v3 a) { return scale(a, 1.0f / length(a)); }
+__host__ __device__ __forceinline__ float length(v3 a) { return sqrtf(dot(a, a)); }
+__host__ __device__ __forceinline__ v3 normalize(v3 a) { return scale(a, 1.0f / length(a)); }
 
 struct Ray { v3 o, d; };
 // linalg.zig:284-286
-__device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + scale(r.d, t); }
+__host__ __device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + scale(r.d, t); }
 
 // @intFromFloat with the oracle's DEFINED semantics: truncation, saturating, NaN -> 0
 // (exactly cvt.rzi.{u32,s32}.f32).
@@ -212,7 +213,7 @@ __device__ __forceinline__ float grid_next(GridIter& it)
 }
 
 // ---- Triangle.rayIntersection (src/linalg.zig:696-722) --------------------------------
-__device__ __forceinline__ bool tri_ray(v3 v0, v3 e1, v3 e2, const Ray& r, float& t, float& u_, float& v_)
+__host__ __device__ __forceinline__ bool tri_ray(v3 v0, v3 e1, v3 e2, const Ray& r, float& t, float& u_, float& v_)
 {
     const v3 p = cross(r.d, e2);
     const float det = dot(e1, p);

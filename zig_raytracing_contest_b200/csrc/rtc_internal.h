@@ -4,6 +4,7 @@
 #pragma once
 #include "../../include/rtc.h"
 #include "rtc_kernels.h"
+#include "rtc_bvh.cuh"
 #include "rtc_geometry_owner.h"
 
 #include <cuda_runtime.h>
@@ -55,6 +56,11 @@ struct rtc_scene {
     uint64_t launches = 0;
     std::vector<cudaEvent_t> timer_events;
     rtc::TraceTimer timer{};
+    rtc::LaunchCache cache{};           // per-device launch state of the traversal kernels
+    // RTC_ACCEL_BVH (rtc_scene_build_bvh): nodes + BVH-ordered {v0,e1,e2} records, in `allocs`
+    bool has_bvh = false;
+    rtc::BvhView bvh{};
+    rtc_bvh_info bvh_info{};
 
     template <typename T>
     int alloc(T** out, size_t count)

@@ -14,12 +14,23 @@ struct TraceTimer {
     uint32_t dropped;      // launches not bracketed because the pool was full
 };
 
+// Launch state that belongs to ONE device (occupancy of the traversal kernels there, the shared-memory carveout set
+// there): lives in the rtc_scene, which is bound to a device.
+struct LaunchCache {
+    int trace_per_sm[2] = { 0, 0 };
+    size_t trace_smem[2] = { ~(size_t)0, ~(size_t)0 };
+    int bvh_per_sm[2] = { 0, 0 };
+};
+
 struct LaunchCfg {
     int sm_count;          // SMs of the device the launch goes to
     cudaStream_t stream;
     bool stats;            // instrumented variant (cells/tris counters)
     TraceTimer* timer;     // may be null
+    LaunchCache* cache;    // never null
 };
+
+struct BvhView;
 
 struct PrimaryOut {
     uint32_t* hit_id;      // num_pixels, source-triangle id or 0xFFFFFFFF (may be null)
@@ -35,7 +46,8 @@ struct PrimaryOut {
     cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevParams& prm,         \
                               bool primary, float4* accum, PrimaryOut out,                            \
                               unsigned long long* counters, const WaveScratch& ws,                    \
-                              const LaunchCfg& cfg, uint32_t* launches);                              \
+                              const LaunchCfg& cfg, uint32_t* launches,                               \
+                              const BvhView* bvh /* null = RTC_ACCEL_GRID */);                        \
     /* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242).                                      */ \
     cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,      \
                                uint8_t* rgb, float* radiance, cudaStream_t stream);                   \

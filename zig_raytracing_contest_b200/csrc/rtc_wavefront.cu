@@ -19,6 +19,7 @@
 // (profiles/r1b_*) showed 16 of 32 lanes active and 25 % occupancy at 128 registers.
 #include "rtc_kernels.h"
 #include "rtc_trav.cuh"
+#include "rtc_bvh.cuh"
 
 #ifndef RTC_NS
 #error "compile with -DRTC_NS=exact or -DRTC_NS=fast"
@@ -75,6 +76,7 @@ __device__ __forceinline__ bool queue_setup(const DevScene& sc, const Ray& r, Qu
     if (!two_level) q.ec |= kTravCellOnly;
     return true;
 }
+template <bool BVH>
 __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const QueuedRay& e)
 {
     // a0 / a1 carry what k_shade reads back (origin + slot, direction + top), a2 / a3 the iterator state only k_trace
@@ -82,10 +84,12 @@ __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const
     // streaming (evict-first) accesses keep them from pushing the scene out of L2.
     __stcs(q.a0 + i, make_float4(e.r.o.x, e.r.o.y, e.r.o.z, __uint_as_float(e.slot)));
     __stcs(q.a1 + i, make_float4(e.r.d.x, e.r.d.y, e.r.d.z, __uint_as_float(e.top)));
+    if (BVH) return;                                    // RTC_ACCEL_BVH: no iterator state, 32 B / ray
     __stcs(q.a2 + i, make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec)));
     __stcs(q.a3 + i, make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.c)));
 }
 // Appends the rays of the lanes with `push` to the queue: one atomic per warp, order within the warp kept.
+template <bool BVH>
 __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, bool push, const QueuedRay& e)
 {
     const uint32_t lane = threadIdx.x & 31u;
@@ -94,7 +98,16 @@ __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, b
     uint32_t base = 0;
     if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(count, (uint32_t)__popc(m));
     base = __shfl_sync(kFull, base, __ffs(m) - 1);
-    if (push) queue_store(q, base + __popc(m & ((1u << lane) - 1u)), e);
+    if (push) queue_store<BVH>(q, base + __popc(m & ((1u << lane) - 1u)), e);
+}
+
+// What a new ray needs before it is queued. Grid: Grid.traceRay's iterator (a ray that misses the grid's box is a
+// miss right away, stage3.zig:159). BVH: nothing — the root's slab test plays that part in k_trace_bvh.
+template <bool BVH>
+__device__ __forceinline__ bool ray_setup(const DevScene& sc, const Ray& r, QueuedRay& q)
+{
+    if (BVH) { q.r = r; return true; }
+    return queue_setup(sc, r, q);
 }
 
 struct Counters { uint32_t rays, cells, tris, hits, paths; };
@@ -126,7 +139,7 @@ __device__ __forceinline__ const uint32_t* stage_coarse(const DevScene& sc)
 // k_gen: one thread per path slot. slot = sample_local * num_pixels + pixel_local, so consecutive lanes are
 // consecutive pixels of a row (coherent primary rays). RNG block 0 of the path = the two jitter draws
 // (stage3.zig:238). PRIMARY: pixel centre, no RNG.
-template <bool PRIMARY>
+template <bool PRIMARY, bool BVH>
 __global__ void __launch_bounds__(kThreads)
 k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam, const __grid_constant__ WaveParams wp,
       const __grid_constant__ WaveScratch ws, PrimaryOut out, unsigned long long* __restrict__ counters)
@@ -157,7 +170,7 @@ k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam
                 }
                 cn.rays += 1;
                 e.slot = slot; e.top = 0u;
-                push = queue_setup(sc, ray, e);
+                push = ray_setup<BVH>(sc, ray, e);
                 if (!push) {                                    // Grid.traceRay -> null: a miss (stage3.zig:159)
                     const v3 sky = env_color(ray.d);
                     leaf = make_float4(sky.x, sky.y, sky.z, __uint_as_float(0u));
@@ -173,7 +186,7 @@ k_gen(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam
             }
             if (!push) __stcs(ws.leaf + slot, leaf);
         }
-        queue_push(ws.q[0], ws.counts, push, e);
+        queue_push<BVH>(ws.q[0], ws.counts, push, e);
     }
     flush_counters(cn, counters);
 }
@@ -312,6 +325,72 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// k_trace_bvh: Scene.traceRay (src/stage3.zig:152-186) over a ray queue with the 8-wide BVH of rtc_bvh.cuh in
+// place of the grid (RTC_ACCEL_BVH). Persistent warps with the same per-lane refill as k_trace; every lane walks
+// its own ray: one bvh_step = pop the nearest pending child, one 80-byte node (five 128-bit loads), eight slab
+// tests on quantised boxes, the triangles of the leaves that were hit (48-byte records, three 128-bit loads) with
+// the reference's Triangle.rayIntersection. The traversal stack lives in shared memory for the first kBvhSmemStack
+// entries of every lane (interleaved by lane: conflict-free) and in local memory beyond.
+#ifndef RTC_BVH_MINB
+#define RTC_BVH_MINB 3
+#endif
+#ifndef RTC_BVH_REFILL
+#define RTC_BVH_REFILL 1
+#endif
+static constexpr uint32_t kBvhRefillMin = RTC_BVH_REFILL;     // refill when at least this many lanes of the warp are idle
+
+template <bool STATS>
+__global__ void __launch_bounds__(kTraceThreads, RTC_BVH_MINB)
+k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ count_ptr, uint32_t* __restrict__ head_ptr,
+            uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t n = __ldg(count_ptr);
+    Counters cn = { 0, 0, 0, 0, 0 };
+    uint32_t next = 0, end = 0;
+    bool exhausted = false, alive = false;
+    uint32_t qi = 0;
+    Ray ray; BvhRay br; BvhTrav s;
+    ray.o = ray.d = splat(0.0f);
+    bvh_ray_init(br, ray.o, ray.d);
+    bvh_trav_begin(s);
+    uint2 stack[kBvhStack];
+    for (;;) {
+        const uint32_t idle = __ballot_sync(kFull, !alive);
+        if (idle != 0u && !exhausted && ((uint32_t)__popc(idle) >= kBvhRefillMin || idle == kFull)) {
+            if (next == end) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(head_ptr, kChunk);
+                base = __shfl_sync(kFull, base, 0);
+                if (base >= n) { exhausted = true; next = end = 0; }
+                else { next = base; end = base + kChunk < n ? base + kChunk : n; }
+            }
+            const uint32_t avail = end - next, want = __popc(idle);
+            const uint32_t take = want < avail ? want : avail;
+            if (!alive && (uint32_t)__popc(idle & lt_mask) < take) {
+                qi = next + __popc(idle & lt_mask);
+                const float4 a0 = __ldcs(q.a0 + qi), a1 = __ldcs(q.a1 + qi);
+                ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
+                bvh_ray_init(br, ray.o, ray.d);
+                bvh_trav_begin(s);
+                alive = true;
+            }
+            next += take;
+        }
+        if (__ballot_sync(kFull, alive) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        if (alive && bvh_step<STATS>(bv, br, ray, s, stack, 1u, cn.cells, cn.tris)) {
+            __stcs(hits + qi, make_uint2(__float_as_uint(s.best_t), s.best_tri));
+            alive = false;
+        }
+    }
+    if (STATS) flush_counters(cn, counters);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Triangle.Data (src/stage3.zig:42-71) as stored on the device: 5 float4 per SOURCE triangle.
 struct TriData { v3 n0, n1, n2; float uv0[2], uv1[2], uv2[2]; uint32_t material; };
 __device__ __forceinline__ TriData load_tri_data(const DevScene& sc, uint32_t src)
@@ -342,7 +421,7 @@ __device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, fl
 // RNG block 1 + bounce of the path: draw 0 = the alpha test (always drawn, stage3.zig:207), draws 1, 2 = the
 // scatter direction. A scattering level pushes (emissive, albedo) for k_accum; an alpha pass-through level
 // (stage3.zig:207-213) consumes a depth level and neither attenuates nor pushes.
-template <bool PRIMARY>
+template <bool PRIMARY, bool BVH>
 __global__ void __launch_bounds__(kThreads)
 k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam, const __grid_constant__ WaveParams wp,
         const __grid_constant__ WaveScratch ws, uint32_t bounce, PrimaryOut out, unsigned long long* __restrict__ counters)
@@ -378,8 +457,10 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                 }
             } else {
                 cn.hits += 1;
-                const float4 ta = __ldg(sc.tri_v0 + h.y), tb = __ldg(sc.tri_e1 + h.y), tc = __ldg(sc.tri_e2 + h.y);
-                float t, u, v;
+                // grid: three SoA arrays indexed by the baked triangle; BVH: one record of three float4 per triangle
+                const size_t hi = (size_t)h.y * sc.tri_mul;
+                const float4 ta = __ldg(sc.tri_v0 + hi), tb = __ldg(sc.tri_e1 + hi), tc = __ldg(sc.tri_e2 + hi);
+                float t, u = 0.0f, v = 0.0f;          // the re-test repeats the winning test bit for bit; defined even if it did not
                 tri_ray(mk(ta.x, ta.y, ta.z), mk(tb.x, tb.y, tb.z), mk(tc.x, tc.y, tc.z), ray, t, u, v);
                 t = __uint_as_float(h.x);
                 const uint32_t src = __float_as_uint(ta.w);
@@ -414,14 +495,14 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                     if (bounce + 1u < wp.max_bounce) {       // depth - 1 > 0: the recursion goes on
                         cn.rays += 1;
                         e.slot = slot; e.top = top;
-                        push = queue_setup(sc, ray, e);
+                        push = ray_setup<BVH>(sc, ray, e);
                         if (!push) leaf = env_color(ray.d);
                     }
                 }
             }
             if (!push) __stcs(ws.leaf + slot, make_float4(leaf.x, leaf.y, leaf.z, __uint_as_float(top)));
         }
-        queue_push(qout, ws.counts + bounce + 1u, push, e);
+        queue_push<BVH>(qout, ws.counts + bounce + 1u, push, e);
     }
     flush_counters(cn, counters);
 }
@@ -488,10 +569,12 @@ static void run_trace(const DevScene& sc, const WaveScratch& ws, uint32_t bounce
 {
     auto kern = k_trace<STATS, CSM>;
     const size_t smem = CSM ? sc.coarse_words * sizeof(uint32_t) : 0;
-    static int per_sm[2] = { 0, 0 };                 // occupancy query cached per coarse-bitmap size class
-    static size_t per_sm_smem[2] = { ~(size_t)0, ~(size_t)0 };
-    if (per_sm_smem[STATS] != smem) {
-        per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); per_sm_smem[STATS] = smem;
+    // occupancy and the shared-memory carveout are per DEVICE state (cudaFuncSetAttribute applies to the current
+    // device): cached in the scene's LaunchCache, not in process-wide statics
+    LaunchCache& lc = *cfg.cache;
+    int* per_sm = lc.trace_per_sm;
+    if (lc.trace_smem[STATS] != smem) {
+        per_sm[STATS] = blocks_per_sm(kern, kTraceThreads, smem); lc.trace_smem[STATS] = smem;
         // Ask for no more shared memory than the resident CTAs use (static + coarse bitmap + 1 KiB the system reserves
         // per CTA), so that the rest of the 256 KiB stays L1: the triangle and cell gathers are what the kernel waits
         // on. +1.2 % on the 5 M-triangle scene, +0.9 % on the atrium; a carveout below the need costs occupancy (-14 %),
@@ -519,9 +602,37 @@ static void run_trace(const DevScene& sc, const WaveScratch& ws, uint32_t bounce
     if (timed) { cudaEventRecord(tm->ev[2 * tm->used + 1], cfg.stream); tm->used += 1; }
 }
 
+template <bool STATS>
+static void run_trace_bvh(const BvhView& bv, const WaveScratch& ws, uint32_t bounce, unsigned long long* counters, const LaunchCfg& cfg)
+{
+    auto kern = k_trace_bvh<STATS>;
+    int& per_sm = cfg.cache->bvh_per_sm[STATS];
+    if (per_sm == 0) per_sm = blocks_per_sm(kern, kTraceThreads, 0);
+    TraceTimer* tm = cfg.timer;
+    const bool timed = tm && tm->used < tm->capacity;
+    if (tm && !timed) tm->dropped += 1;
+    if (timed) cudaEventRecord(tm->ev[2 * tm->used], cfg.stream);
+    kern<<<cfg.sm_count * per_sm, kTraceThreads, 0, cfg.stream>>>(bv, ws.q[bounce & 1u], ws.counts + bounce,
+                                                                   ws.counts + kMaxBounce + 1 + bounce, ws.hits, counters);
+    if (timed) { cudaEventRecord(tm->ev[2 * tm->used + 1], cfg.stream); tm->used += 1; }
+}
+
+template <bool PRIMARY, bool BVH>
+static void run_gen(uint32_t g, const DevScene& sc, const DevCamera& cam, const WaveParams& wp, const WaveScratch& ws,
+                    PrimaryOut out, unsigned long long* counters, cudaStream_t st)
+{
+    k_gen<PRIMARY, BVH><<<g, kThreads, 0, st>>>(sc, cam, wp, ws, out, counters);
+}
+template <bool PRIMARY, bool BVH>
+static void run_shade(uint32_t g, const DevScene& sc, const DevCamera& cam, const WaveParams& wp, const WaveScratch& ws,
+                      uint32_t b, PrimaryOut out, unsigned long long* counters, cudaStream_t st)
+{
+    k_shade<PRIMARY, BVH><<<g, kThreads, 0, st>>>(sc, cam, wp, ws, b, out, counters);
+}
+
 cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevParams& prm, bool primary, float4* accum,
                           PrimaryOut out, unsigned long long* counters, const WaveScratch& ws, const LaunchCfg& cfg,
-                          uint32_t* launches)
+                          uint32_t* launches, const BvhView* bvh)
 {
     if (prm.num_pixels == 0 || (!primary && prm.num_samples == 0)) return cudaSuccess;
     const uint32_t S = primary ? 1u : prm.num_samples;
@@ -545,14 +656,15 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
             const uint32_t nslots = wp.num_pixels * wp.ns;
             const uint32_t need = (nslots + kThreads - 1) / kThreads;
             const uint32_t g = need < (uint32_t)wide ? need : (uint32_t)wide;
-            if (primary) k_gen<true><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, out, counters);
-            else         k_gen<false><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, out, counters);
+            if (bvh) { if (primary) run_gen<true, true>(g, sc, cam, wp, ws, out, counters, cfg.stream); else run_gen<false, true>(g, sc, cam, wp, ws, out, counters, cfg.stream); }
+            else     { if (primary) run_gen<true, false>(g, sc, cam, wp, ws, out, counters, cfg.stream); else run_gen<false, false>(g, sc, cam, wp, ws, out, counters, cfg.stream); }
             *launches += 1;
             for (uint32_t b = 0; b < B; ++b) {
-                if (csm) { if (cfg.stats) run_trace<true, true>(sc, ws, b, counters, cfg); else run_trace<false, true>(sc, ws, b, counters, cfg); }
+                if (bvh) { if (cfg.stats) run_trace_bvh<true>(*bvh, ws, b, counters, cfg); else run_trace_bvh<false>(*bvh, ws, b, counters, cfg); }
+                else if (csm) { if (cfg.stats) run_trace<true, true>(sc, ws, b, counters, cfg); else run_trace<false, true>(sc, ws, b, counters, cfg); }
                 else     { if (cfg.stats) run_trace<true, false>(sc, ws, b, counters, cfg); else run_trace<false, false>(sc, ws, b, counters, cfg); }
-                if (primary) k_shade<true><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, b, out, counters);
-                else         k_shade<false><<<g, kThreads, 0, cfg.stream>>>(sc, cam, wp, ws, b, out, counters);
+                if (bvh) { if (primary) run_shade<true, true>(g, sc, cam, wp, ws, b, out, counters, cfg.stream); else run_shade<false, true>(g, sc, cam, wp, ws, b, out, counters, cfg.stream); }
+                else     { if (primary) run_shade<true, false>(g, sc, cam, wp, ws, b, out, counters, cfg.stream); else run_shade<false, false>(g, sc, cam, wp, ws, b, out, counters, cfg.stream); }
                 *launches += 2;
             }
             k_accum<<<(wp.num_pixels + kThreads - 1) / kThreads, kThreads, 0, cfg.stream>>>(wp, ws, accum);

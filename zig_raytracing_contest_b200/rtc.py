@@ -49,6 +49,7 @@ def lib():
                                         C.c_void_p, C.c_void_p]
     L.rtc_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
+    L.rtc_scene_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.BvhInfo)]
     L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
     L.rtc_geometry_build_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int,
                                             C.POINTER(abi.Geometry)]
@@ -247,12 +248,12 @@ def make_scene_desc(geometry, materials):
 
 def make_params(num_samples=3, max_bounce=4, mode=abi.RTC_MODE_PATH, seed=0, sample_offset=0,
                 total_samples=0, math=abi.RTC_MATH_EXACT, tile_rank=0, tile_world=0, collect_stats=False,
-                tile_rows=0):
+                tile_rows=0, accel=abi.RTC_ACCEL_GRID):
     """main.Config's num_samples / max_bounce (src/main.zig:56-61; config.json defaults 3 and 4)."""
     p = abi.Params()
     p.num_samples, p.max_bounce, p.mode, p.seed = num_samples, max_bounce, mode, seed
     p.sample_offset, p.total_samples = sample_offset, total_samples
-    p.accel, p.math = abi.RTC_ACCEL_GRID, math
+    p.accel, p.math = accel, math
     p.tile_rank, p.tile_world, p.collect_stats = tile_rank, tile_world, 1 if collect_stats else 0
     p.tile_rows = tile_rows
     return p
@@ -342,6 +343,12 @@ class Scene:
         """Adds params.num_samples samples per pixel into a device float4 accumulator (async)."""
         _check(lib().rtc_render_accumulate(self._h, C.byref(camera), C.byref(params),
                                            C.c_void_p(d_accum_ptr), C.c_void_p(stream_ptr or 0)))
+
+    def build_bvh(self, num_threads=0):
+        """RTC_ACCEL_BVH's structure, ahead of the first render that asks for it (rtc_scene_build_bvh)."""
+        info = abi.BvhInfo()
+        _check(lib().rtc_scene_build_bvh(self._h, int(num_threads), C.byref(info)))
+        return {k: getattr(info, k) for k, _ in info._fields_ if k != "reserved"}
 
     def stats(self):
         st = abi.Stats()
