@@ -154,6 +154,14 @@ def texture_sample(tex, u, v):
     return out
 
 
+def interpolate(tri_data_record, u, v):
+    """Triangle.Data.interpolate for the normal and the texcoord of one TRI_DATA_DTYPE record."""
+    rec = np.ascontiguousarray(tri_data_record, dtype=TRI_DATA_DTYPE).reshape(1)
+    n, t = np.zeros(3, np.float32), np.zeros(2, np.float32)
+    lib().orc_interpolate(rec.ctypes.data_as(C.c_void_p), C.c_float(u), C.c_float(v), _fp(n), _fp(t))
+    return n, t
+
+
 def to_rgb(c):
     c = _f(c)
     out = np.zeros(3, np.uint8)

@@ -758,6 +758,13 @@ static inline void interp_texcoord(const rtc_tri_data* d, float u, float v, floa
     out[1] = d->texcoord[0][1] * w + d->texcoord[1][1] * u + d->texcoord[2][1] * v;
 }
 
+/* unit-level entry for the known-answer tests (tests/test_oracle_kat.py) */
+void orc_interpolate(const rtc_tri_data* d, float u, float v, float normal_out[3], float uv_out[2])
+{
+    v3_to(interp_normal(d, u, v), normal_out);
+    interp_texcoord(d, u, v, uv_out);
+}
+
 typedef struct {
     const rtc_scene_desc* scene;
     uint64_t seed;

@@ -74,6 +74,8 @@ int   orc_triangle_ray_intersection(const float v0[3], const float e1[3], const 
                                     float* t, float* u, float* v);
 int   orc_triangle_aabb(const float tri[9], const float bmin[3], const float bmax[3]);
 void  orc_texture_sample(const rtc_texture* tex, float u, float v, float* out /* channels */);
+/* Triangle.Data.interpolate (stage3.zig:53-71) for both field types */
+void  orc_interpolate(const rtc_tri_data* d, float u, float v, float normal_out[3], float uv_out[2]);
 void  orc_to_rgb(const float c[3], uint8_t out[3]);
 void  orc_env_color(const float dir[3], float out[3]);
 void  orc_camera_get_ray(const rtc_camera* cam, float x, float y, float orig[3], float dir[3]);
