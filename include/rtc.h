@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 7u
+#define RTC_ABI_VERSION 8u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -145,6 +145,17 @@ enum {
     RTC_MATH_FAST = 1
 };
 
+/* Partition of ONE frame over several GPUs; the scene is replicated on every device. The reference's own
+ * split is contiguous pixel ranges per worker thread with no communication (src/stage3.zig:228-233,247-255). */
+enum {
+    RTC_SHARD_STRIPS = 0,   /* strips of tile_rows (0 = 8) full rows dealt round-robin over the devices (sky rows and
+                               geometry rows spread over all of them). Every device resolves its own strips to RGB8.
+                               Frame bit-identical to the one-GPU frame. */
+    RTC_SHARD_SAMPLES = 1   /* device g renders samples [g*S/N, (g+1)*S/N) of every pixel; the float accumulators are
+                               summed in device order. Equal to the one-GPU frame to fp32 summation order (RGB8 +-1). */
+};
+#define RTC_MAX_GPUS 16
+
 /* main.Config (src/main.zig:56-61) + what the CLI adds. num_samples/max_bounce are the
  * two hot-loop trip counts (src/stage3.zig:237,239). */
 typedef struct rtc_params {
@@ -161,7 +172,16 @@ typedef struct rtc_params {
     uint32_t collect_stats;  /* nonzero: run the instrumented kernels, fill rtc_aux.stats           */
     uint32_t tile_rows;      /* 0: one contiguous band of rows per rank, rows [h*r/n, h*(r+1)/n);   */
                              /* k>0: strips of k full rows dealt round-robin, strip i -> rank i % n */
+    int32_t  num_gpus;       /* rtc_render: 0 / 1 = the scene's device. N > 1: this ONE blocking call (the shape of   */
+                             /* src/main.zig:126) renders the frame on N devices of this process — the scene's device */
+                             /* first, then the other sm_100 devices in index order; replicas are made on first use   */
+                             /* by peer copies. With N > 1 the tile_* / sample_offset / total_samples fields must be 0 */
+    uint32_t shard;          /* RTC_SHARD_*: the partition num_gpus > 1 and rtc_render_sharded use                    */
 } rtc_params;
+
+/* Limits narrower than the reference's types, all reported as RTC_ERR_UNSUPPORTED: max_bounce <= 64 (the reference's
+ * field is u16; the kernels keep one queue counter per bounce), grid_resolution <= 1024 per axis (packed cell word),
+ * fewer than 2^31 pixels, fewer than 2^32 baked triangles. */
 
 /* Counters behind SURVEY §8(d)'s bytes-per-ray figure. */
 typedef struct rtc_stats {
@@ -175,6 +195,8 @@ typedef struct rtc_stats {
     double   trace_ms;       /* summed device time of the traversal kernel launches in that span  */
     uint32_t trace_launches; /* ... how many launches that sum covers                            */
     uint32_t trace_launches_untimed;
+    double   frame_ms;       /* device time of the whole call on this device's stream: render kernels + combining the  */
+                             /* shards + resolve, up to (not including) the copy of the frame to the host              */
 } rtc_stats;
 
 /* Optional extra outputs (any pointer may be NULL). Host pointers. */
@@ -201,10 +223,38 @@ void rtc_scene_destroy(rtc_scene* scene);
 int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
                uint8_t* rgb_out, rtc_aux* aux);
 
+/* ---- one process per GPU (MPI- / torchrun-style hosts): the same sharded frame, combined with NCCL ------------- */
+
+/* A communicator over `world` processes, each driving one device. rank 0 makes an id, the host hands the bytes to every
+ * rank by its own means (MPI_Bcast, torch.distributed, a file), every rank calls rtc_comm_create (collective:
+ * ncclCommInitRank). NCCL is loaded at run time (libnccl.so.2); RTC_ERR_UNSUPPORTED when it cannot be. */
+typedef struct rtc_comm rtc_comm;
+#define RTC_COMM_ID_BYTES 128
+int  rtc_comm_unique_id(uint8_t id_out[RTC_COMM_ID_BYTES]);
+int  rtc_comm_create(const uint8_t id[RTC_COMM_ID_BYTES], int rank, int world, int device, rtc_comm** out);
+void rtc_comm_destroy(rtc_comm* comm);
+
+/* scene.render for a frame sharded over the ranks of `comm` (NULL = this process alone). Collective and blocking: every
+ * rank passes its replica of the scene, the same camera and the same params (params->shard picks the partition, num_gpus
+ * and the tile_* / sample_* fields are ignored). STRIPS: every rank resolves its strips, rank 0 receives them
+ * (ncclSend / ncclRecv) and assembles the frame. SAMPLES: one ncclReduce(sum) of the rgb accumulators to rank 0, which
+ * resolves. rank 0 gets the frame in rgb_out (host, w*h*3); with rgb_out NULL the finished RGB8 frame stays in device
+ * memory of rank 0 and nothing is copied to the host. aux (may be NULL): stats are per rank; radiance / hits on rank 0 are
+ * not filled by this entry point. */
+int  rtc_render_sharded(rtc_scene* scene, rtc_comm* comm, const rtc_camera* camera, const rtc_params* params,
+                        uint8_t* rgb_out, rtc_aux* aux);
+
+/* Makes `stream` (a cudaStream_t; NULL = back to the scene's own stream) the stream every later call on this scene
+ * launches on — a host that brackets frames with its own CUDA events, or orders them against its own work, passes its
+ * stream here. A scene allows ONE stream in flight at a time: its ray queues, counters and timer events are per scene,
+ * so calls on one scene must not overlap (this holds for rtc_render_accumulate's stream argument too). */
+int  rtc_scene_set_stream(rtc_scene* scene, void* stream);
+
 /* ---- device-resident pieces of the same path (multi-GPU plumbing, benchmarking) --- */
 
 /* Adds this call's samples into d_accum (device, w*h float4: rgb sum + sample count),
- * asynchronously on `stream` (a cudaStream_t, NULL = default stream). */
+ * asynchronously on `stream` (a cudaStream_t, NULL = default stream). Calls on one scene must not overlap (see
+ * rtc_scene_set_stream): the wavefront scratch is per scene. */
 int rtc_render_accumulate(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
                           void* d_accum, void* stream);
 

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_sizes_match_header_layout():
     assert C.sizeof(abi.Grid) == 48 and C.sizeof(abi.Cell) == 8 and C.sizeof(abi.TriPos) == 48
     assert C.sizeof(abi.TriData) == 68 and C.sizeof(abi.Texture) == 40 and C.sizeof(abi.Material) == 120
-    assert C.sizeof(abi.Camera) == 56 and C.sizeof(abi.Params) == 48 and C.sizeof(abi.Stats) == 72
+    assert C.sizeof(abi.Camera) == 56 and C.sizeof(abi.Params) == 56 and C.sizeof(abi.Stats) == 80
 
 
 def _has_gpu():

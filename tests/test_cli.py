@@ -230,8 +230,9 @@ def test_cli_renders_the_same_frame_as_the_binding(tmp_path):
     json.dump(CONFIG, open(str(tmp_path / "config.json"), "w"))
     r = _run_cli(tmp_path, "--in", "room.glb", "--out=frame.png", "--camera", "Camera 1", "--height", "72", "--seed", "5")
     assert r.returncode == 0, r.stderr
-    for phase in ("Loaded, preprocessed and compiled in", "triangle assembly", "Rendered in", "Saved in", "Done in"):
-        assert phase in r.stderr
+    # the reference's six phase lines, in its order (src/main.zig:106,113,119,127,141,142)
+    pos = [r.stderr.find("info: %s in " % p) for p in ("Loaded", "Preprocessed", "Compiled", "Rendered", "Saved", "Done")]
+    assert all(p >= 0 for p in pos) and pos == sorted(pos), r.stderr
     got = rtc.png_read(str(tmp_path / "frame.png"))
     for env in ({"RTC_HOST_LOAD": "1"}, {"RTC_HOST_BUILD": "1"}):      # stage1 / stage1+2 on the host: same frame
         r = _run_cli(tmp_path, "--in", "room.glb", "--out=host.png", "--camera", "Camera 1", "--height", "72", "--seed", "5", env=env)

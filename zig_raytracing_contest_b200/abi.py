@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 7
+RTC_ABI_VERSION = 8
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -20,6 +20,10 @@ RTC_MODE_PATH = 0
 RTC_MODE_PRIMARY = 1
 RTC_ACCEL_GRID = 0
 RTC_ACCEL_BVH = 1
+RTC_SHARD_STRIPS = 0
+RTC_SHARD_SAMPLES = 1
+RTC_MAX_GPUS = 16
+RTC_COMM_ID_BYTES = 128
 RTC_MATH_EXACT = 0
 RTC_MATH_FAST = 1
 
@@ -81,14 +85,16 @@ class Params(C.Structure):        # rtc_params
                 ("sample_offset", C.c_uint32), ("total_samples", C.c_uint32),
                 ("accel", C.c_uint32), ("math", C.c_uint32),
                 ("tile_rank", C.c_uint32), ("tile_world", C.c_uint32),
-                ("collect_stats", C.c_uint32), ("tile_rows", C.c_uint32)]
+                ("collect_stats", C.c_uint32), ("tile_rows", C.c_uint32),
+                ("num_gpus", C.c_int32), ("shard", C.c_uint32)]
 
 
 class Stats(C.Structure):         # rtc_stats
     _fields_ = [("rays", C.c_uint64), ("cells_visited", C.c_uint64),
                 ("tris_tested", C.c_uint64), ("hits_shaded", C.c_uint64),
                 ("paths", C.c_uint64), ("kernel_ms", C.c_double), ("launches", C.c_uint64),
-                ("trace_ms", C.c_double), ("trace_launches", C.c_uint32), ("trace_launches_untimed", C.c_uint32)]
+                ("trace_ms", C.c_double), ("trace_launches", C.c_uint32), ("trace_launches_untimed", C.c_uint32),
+                ("frame_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -136,7 +142,8 @@ class HostScene(C.Structure):     # rtc_host_scene
 # Every symbol include/rtc.h declares (checked by tests/test_abi.py against the built library).
 EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
-    "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_geometry_build", "rtc_geometry_free",
+    "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_scene_set_stream",
+    "rtc_comm_unique_id", "rtc_comm_create", "rtc_comm_destroy", "rtc_render_sharded", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_geometry_build_device", "rtc_scene_create_from_soup",
     "rtc_scene_create_from_gltf", "rtc_gltf_load_device",
     "rtc_last_error", "rtc_abi_version", "rtc_device_count",

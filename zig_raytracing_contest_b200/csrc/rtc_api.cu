@@ -234,9 +234,12 @@ int rtc_scene_finish_(rtc_scene* s)
     if (int rc = s->alloc(&s->counters, (size_t)rtc::CNT_N)) return rc;
     if (int rc = s->alloc(&s->work, (size_t)4)) return rc;
     CU(cudaMemset(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long)));
-    CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
+    s->stream = s->own_stream;
     CU(cudaEventCreate(&s->ev0));
     CU(cudaEventCreate(&s->ev1));
+    CU(cudaEventCreate(&s->ev_frame));
+    CU(cudaEventCreateWithFlags(&s->ev_part, cudaEventDisableTiming));
     s->timer_events.resize(2 * 4096);
     for (cudaEvent_t& e : s->timer_events) CU(cudaEventCreate(&e));
     s->timer.ev = s->timer_events.data(); s->timer.capacity = 4096; s->timer.used = 0; s->timer.dropped = 0;
@@ -248,14 +251,19 @@ void rtc_scene_free_(rtc_scene* s)
     if (!s) return;
     DeviceGuard guard(s->device);
     cudaDeviceSynchronize();
-    for (void* p : s->allocs) cudaFree(p);
+    for (rtc_scene* r : s->replicas) rtc_scene_free_(r);
+    s->replicas.clear();
+    for (const rtc_scene::Alloc& a : s->allocs) cudaFree(a.p);
     for (void* p : s->wave_allocs) cudaFree(p);
     cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     for (cudaEvent_t e : s->timer_events) cudaEventDestroy(e);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->ev_part) cudaEventDestroy(s->ev_part);
+    if (s->ev_frame) cudaEventDestroy(s->ev_frame);
+    if (s->own_stream) cudaStreamDestroy(s->own_stream);
+    cudaFree(s->d_stage);
     delete s;
 }
 
@@ -313,7 +321,9 @@ rtc::DevCamera to_dev(const rtc_camera& c)
     return d;
 }
 
-int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_params* p)
+}  // namespace
+
+int rtc_check_render_args_(const rtc_scene* s, const rtc_camera* cam, const rtc_params* p)
 {
     if (!s || !cam || !p) return fail(RTC_ERR_INVALID_ARGUMENT, "null scene, camera or params");
     if (cam->w == 0 || cam->h == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "camera has zero size");
@@ -324,8 +334,15 @@ int check_render_args(const rtc_scene* s, const rtc_camera* cam, const rtc_param
     if (p->mode == RTC_MODE_PATH && p->max_bounce > rtc::kMaxBounce)
         return fail(RTC_ERR_UNSUPPORTED, "max_bounce %u > %u (per-bounce queue bookkeeping of the kernels)", (unsigned)p->max_bounce, rtc::kMaxBounce);
     if (p->tile_world > 1 && p->tile_rank >= p->tile_world) return fail(RTC_ERR_INVALID_ARGUMENT, "tile_rank %u >= tile_world %u", p->tile_rank, p->tile_world);
+    if (p->num_gpus < 0 || p->num_gpus > RTC_MAX_GPUS) return fail(RTC_ERR_INVALID_ARGUMENT, "num_gpus %d outside 0..%d", p->num_gpus, RTC_MAX_GPUS);
+    if (p->shard != RTC_SHARD_STRIPS && p->shard != RTC_SHARD_SAMPLES) return fail(RTC_ERR_INVALID_ARGUMENT, "unknown shard %u", p->shard);
+    if (p->num_gpus > 1 && (p->tile_world > 1 || p->sample_offset != 0 || (p->total_samples != 0 && p->total_samples != p->num_samples)))
+        return fail(RTC_ERR_INVALID_ARGUMENT, "num_gpus > 1 shards the frame itself: tile_rank/tile_world/sample_offset/total_samples must be unset");
     return RTC_OK;
 }
+
+namespace {
+#define check_render_args rtc_check_render_args_
 
 // The pixels of the frame that this call renders (partitioning A). tile_world <= 1: all.
 // tile_rows == 0: one contiguous band of rows per rank, rank r of n owns rows [r*h/n, (r+1)*h/n) (the reference's
@@ -447,24 +464,43 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
     return RTC_OK;
 }
 
-int ensure_frame(rtc_scene* s, uint32_t pixels)
+}  // namespace
+
+int rtc_ensure_frame_(rtc_scene* s, uint32_t pixels)
 {
     if (pixels <= s->cap_pixels) return RTC_OK;
     cudaFree(s->accum); cudaFree(s->d_rgb); cudaFree(s->d_radiance); cudaFree(s->d_hit_id); cudaFree(s->d_hit_tuv);
-    if (s->h_pinned) cudaFreeHost(s->h_pinned);
     s->accum = nullptr; s->d_rgb = nullptr; s->d_radiance = nullptr; s->d_hit_id = nullptr; s->d_hit_tuv = nullptr;
-    s->h_pinned = nullptr; s->cap_pixels = 0;
+    s->cap_pixels = 0;
     CU(cudaMalloc(&s->accum, (size_t)pixels * sizeof(float4)));
     CU(cudaMalloc(&s->d_rgb, (size_t)pixels * 3));
     CU(cudaMalloc(&s->d_radiance, (size_t)pixels * 3 * sizeof(float)));
     CU(cudaMalloc(&s->d_hit_id, (size_t)pixels * sizeof(uint32_t)));
     CU(cudaMalloc(&s->d_hit_tuv, (size_t)pixels * 3 * sizeof(float)));
-    s->h_pinned_bytes = (size_t)pixels * (3 + 12 + 4 + 12);
-    CU(cudaMallocHost(&s->h_pinned, s->h_pinned_bytes));
     s->cap_pixels = pixels;
     return RTC_OK;
 }
 
+// The pinned host frame: radiance | hit_tuv | hit_id | rgb (every section 4-byte aligned). Portable, so that every
+// device of a multi-GPU render can copy into it.
+int rtc_ensure_host_frame_(rtc_scene* s, uint32_t pixels, RtcHostFrame* hf)
+{
+    if (pixels > s->h_pinned_pixels) {
+        if (s->h_pinned) cudaFreeHost(s->h_pinned);
+        s->h_pinned = nullptr; s->h_pinned_pixels = 0;
+        s->h_pinned_bytes = (size_t)pixels * (12 + 12 + 4 + 3);
+        CU(cudaHostAlloc(&s->h_pinned, s->h_pinned_bytes, cudaHostAllocPortable));
+        s->h_pinned_pixels = pixels;
+    }
+    const size_t P = s->h_pinned_pixels;
+    hf->radiance = reinterpret_cast<float*>(s->h_pinned);
+    hf->hit_tuv = reinterpret_cast<float*>(s->h_pinned + 12 * P);
+    hf->hit_id = reinterpret_cast<uint32_t*>(s->h_pinned + 24 * P);
+    hf->rgb = s->h_pinned + 28 * P;
+    return RTC_OK;
+}
+
+namespace {
 int read_counters(rtc_scene* s, rtc_stats* out)
 {
     unsigned long long c[rtc::CNT_N];
@@ -491,76 +527,98 @@ int read_counters(rtc_scene* s, rtc_stats* out)
 
 }  // namespace
 
-extern "C" {
+int rtc_read_counters_(rtc_scene* s, rtc_stats* out) { return read_counters(s, out); }
 
-int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t* rgb_out, rtc_aux* aux)
+int rtc_render_part_(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint32_t total, const RtcHostFrame& hf,
+                     bool want_hits, bool resolve_and_fetch, bool clear_counters)
 {
-    if (int rc = check_render_args(s, cam, p)) return rc;
-    if (!rgb_out) return fail(RTC_ERR_INVALID_ARGUMENT, "rgb_out is null");
-    DeviceGuard guard(s->device);
     const uint32_t pixels = cam->w * cam->h;
-    if (int rc = ensure_frame(s, pixels)) return rc;
-    const uint32_t total = p->mode == RTC_MODE_PRIMARY ? 1u : (p->total_samples ? p->total_samples : p->num_samples);
-    if (total == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "num_samples is zero");
+    if (int rc = rtc_ensure_frame_(s, pixels)) return rc;
     const Shard sh = shard_pixels(cam, p);
     // the span of the frame buffers this call touches: its band, or (interleaved strips) the whole frame
     const bool strips = sh.stride_px != 0;
     const size_t first = strips ? 0 : sh.first, count = strips ? pixels : sh.count;
-    const bool want_hits = p->mode == RTC_MODE_PRIMARY && aux && (aux->hit_id || aux->hit_tuv);
-    const bool want_rad = aux && aux->radiance;
     cudaStream_t st = s->stream;
-    if (aux && aux->stats) CU(cudaMemsetAsync(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long), st));
-    CU(cudaMemsetAsync(s->accum + first, 0, count * sizeof(float4), st));
+    if (clear_counters) CU(cudaMemsetAsync(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long), st));
+    if (count) CU(cudaMemsetAsync(s->accum + first, 0, count * sizeof(float4), st));
     CU(cudaEventRecord(s->ev0, st));
     rtc::PrimaryOut pout; pout.hit_id = want_hits ? s->d_hit_id : nullptr; pout.hit_tuv = want_hits ? s->d_hit_tuv : nullptr;
     if (int rc = launch_render(s, cam, p, s->accum, pout, st)) return rc;
+    if (!resolve_and_fetch) { CU(cudaEventRecord(s->ev1, st)); return RTC_OK; }
+    const bool want_rad = hf.radiance != nullptr;
     cudaError_t e = p->math == RTC_MATH_FAST
         ? rtc::fast::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st)
         : rtc::exact::launch_resolve(s->accum + first, (uint32_t)count, total, s->d_rgb + 3 * first, want_rad ? s->d_radiance + 3 * first : nullptr, st);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "resolve launch: %s", cudaGetErrorString(e));
     s->launches += 1;
     CU(cudaEventRecord(s->ev1, st));
-    // D2H of this call's pixels through the pinned staging buffer (rgb_out is pageable caller memory,
-    // src/main.zig:122), compacted: a band is one copy, interleaved strips are one strided 2-D copy (+ the short tail).
-    uint8_t* h_rgb = s->h_pinned;
-    uint8_t* h_rad = s->h_pinned + (size_t)pixels * 3;
-    uint8_t* h_id = s->h_pinned + (size_t)pixels * 15;
-    uint8_t* h_tuv = s->h_pinned + (size_t)pixels * 19;
-    auto fetch = [&](const void* d_base, size_t elem, uint8_t* stage) -> cudaError_t {
+    // D2H of this call's pixels to their FINAL place in the pinned frame: a band is one copy, interleaved strips are one
+    // 2-D copy strided on both sides (+ the short tail)
+    auto fetch = [&](const void* d_base, size_t elem, void* h_base) -> cudaError_t {
         const uint8_t* src = (const uint8_t*)d_base + elem * sh.first;
-        if (!strips) return cudaMemcpyAsync(stage, src, elem * sh.count, cudaMemcpyDeviceToHost, st);
+        uint8_t* dst = (uint8_t*)h_base + elem * sh.first;
+        if (!strips) return cudaMemcpyAsync(dst, src, elem * sh.count, cudaMemcpyDeviceToHost, st);
         cudaError_t r = cudaSuccess;
         if (sh.full_strips)
-            r = cudaMemcpy2DAsync(stage, elem * sh.strip_px, src, elem * sh.stride_px, elem * sh.strip_px, sh.full_strips, cudaMemcpyDeviceToHost, st);
+            r = cudaMemcpy2DAsync(dst, elem * sh.stride_px, src, elem * sh.stride_px, elem * sh.strip_px, sh.full_strips, cudaMemcpyDeviceToHost, st);
         if (r == cudaSuccess && sh.tail_px)
-            r = cudaMemcpyAsync(stage + elem * sh.strip_px * sh.full_strips, src + elem * (size_t)sh.stride_px * sh.full_strips,
+            r = cudaMemcpyAsync(dst + elem * (size_t)sh.stride_px * sh.full_strips, src + elem * (size_t)sh.stride_px * sh.full_strips,
                                 elem * sh.tail_px, cudaMemcpyDeviceToHost, st);
         return r;
     };
-    auto scatter = [&](void* host_base, size_t elem, const uint8_t* stage) {
-        uint8_t* dst = (uint8_t*)host_base + elem * sh.first;
-        if (!strips) { memcpy(dst, stage, elem * sh.count); return; }
-        for (uint32_t k = 0; k < sh.full_strips; ++k) memcpy(dst + elem * (size_t)sh.stride_px * k, stage + elem * (size_t)sh.strip_px * k, elem * sh.strip_px);
-        if (sh.tail_px) memcpy(dst + elem * (size_t)sh.stride_px * sh.full_strips, stage + elem * (size_t)sh.strip_px * sh.full_strips, elem * sh.tail_px);
+    if (sh.count) {
+        if (hf.rgb) CU(fetch(s->d_rgb, 3, hf.rgb));
+        if (want_rad) CU(fetch(s->d_radiance, 12, hf.radiance));
+        if (want_hits && hf.hit_id) CU(fetch(s->d_hit_id, 4, hf.hit_id));
+        if (want_hits && hf.hit_tuv) CU(fetch(s->d_hit_tuv, 12, hf.hit_tuv));
+    }
+    return RTC_OK;
+}
+
+void rtc_copy_out_(const rtc_camera* cam, const rtc_params* p, const RtcHostFrame& hf, uint8_t* rgb_out, rtc_aux* aux, bool want_hits)
+{
+    const Shard sh = shard_pixels(cam, p);
+    if (!sh.count) return;
+    const bool strips = sh.stride_px != 0;
+    auto copy = [&](void* user, size_t elem, const void* pinned) {
+        uint8_t* dst = (uint8_t*)user + elem * sh.first;
+        const uint8_t* src = (const uint8_t*)pinned + elem * sh.first;
+        if (!strips) { memcpy(dst, src, elem * sh.count); return; }
+        for (uint32_t k = 0; k < sh.full_strips; ++k) memcpy(dst + elem * (size_t)sh.stride_px * k, src + elem * (size_t)sh.stride_px * k, elem * sh.strip_px);
+        if (sh.tail_px) memcpy(dst + elem * (size_t)sh.stride_px * sh.full_strips, src + elem * (size_t)sh.stride_px * sh.full_strips, elem * sh.tail_px);
     };
-    if (sh.count) {
-        CU(fetch(s->d_rgb, 3, h_rgb));
-        if (want_rad) CU(fetch(s->d_radiance, 12, h_rad));
-        if (want_hits && aux->hit_id) CU(fetch(s->d_hit_id, 4, h_id));
-        if (want_hits && aux->hit_tuv) CU(fetch(s->d_hit_tuv, 12, h_tuv));
-    }
-    CU(cudaStreamSynchronize(st));
-    if (sh.count) {
-        scatter(rgb_out, 3, h_rgb);
-        if (want_rad) scatter(aux->radiance, 12, h_rad);
-        if (want_hits && aux->hit_id) scatter(aux->hit_id, 4, h_id);
-        if (want_hits && aux->hit_tuv) scatter(aux->hit_tuv, 12, h_tuv);
-    }
+    if (rgb_out && hf.rgb) copy(rgb_out, 3, hf.rgb);
+    if (aux && aux->radiance && hf.radiance) copy(aux->radiance, 12, hf.radiance);
+    if (want_hits && aux && aux->hit_id && hf.hit_id) copy(aux->hit_id, 4, hf.hit_id);
+    if (want_hits && aux && aux->hit_tuv && hf.hit_tuv) copy(aux->hit_tuv, 12, hf.hit_tuv);
+}
+
+extern "C" {
+
+int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, uint8_t* rgb_out, rtc_aux* aux)
+{
+    if (int rc = check_render_args(s, cam, p)) return rc;
+    if (!rgb_out) return fail(RTC_ERR_INVALID_ARGUMENT, "rgb_out is null");
+    if (p->num_gpus > 1) return rtc_render_multi_(s, cam, p, rgb_out, aux);
+    DeviceGuard guard(s->device);
+    const uint32_t pixels = cam->w * cam->h;
+    const uint32_t total = p->mode == RTC_MODE_PRIMARY ? 1u : (p->total_samples ? p->total_samples : p->num_samples);
+    if (total == 0) return fail(RTC_ERR_INVALID_ARGUMENT, "num_samples is zero");
+    const bool want_hits = p->mode == RTC_MODE_PRIMARY && aux && (aux->hit_id || aux->hit_tuv);
+    RtcHostFrame hf;
+    if (int rc = rtc_ensure_host_frame_(s, pixels, &hf)) return rc;
+    if (!(aux && aux->radiance)) hf.radiance = nullptr;
+    if (!(want_hits && aux->hit_id)) hf.hit_id = nullptr;
+    if (!(want_hits && aux->hit_tuv)) hf.hit_tuv = nullptr;
+    if (int rc = rtc_render_part_(s, cam, p, total, hf, want_hits, true, aux && aux->stats)) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    rtc_copy_out_(cam, p, hf, rgb_out, aux, want_hits);
     if (aux && aux->stats) {
         if (int rc = read_counters(s, aux->stats)) return rc;
         float ms = 0.0f;
         CU(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         aux->stats->kernel_ms = ms;
+        aux->stats->frame_ms = ms;
     }
     return RTC_OK;
 }

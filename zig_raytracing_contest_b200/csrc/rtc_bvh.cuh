@@ -38,8 +38,9 @@ struct BvhView {
 };
 
 struct BvhRay {
-    float ox, oy, oz, dx, dy, dz;
-    float ix, iy, iz;          // 1 / d, with |d| below 2^-80 replaced by +-2^-80 (no 0 * inf in the slab test)
+    float ox, oy, oz;
+    float ix, iy, iz;          // 1 / d, with |d| below 2^-80 replaced by +-2^-80 (no 0 * inf in the slab test);
+                               // the sign of 1/d is the sign of d (-0.0 included), which is all the slab test needs of d
     uint32_t octinv4;          // (7 ^ octant) replicated into the four bytes
 };
 
@@ -80,13 +81,13 @@ RTC_HD float bvh_fma(float a, float b, float c)
 
 RTC_HD void bvh_ray_init(BvhRay& r, v3 o, v3 d)
 {
-    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.ox = o.x; r.oy = o.y; r.oz = o.z;
     const float tiny = bvh_u2f((127u - 80u) << 23);
     const float ax = fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x);
     const float ay = fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y);
     const float az = fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z);
     r.ix = 1.0f / ax; r.iy = 1.0f / ay; r.iz = 1.0f / az;
-    const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    const uint32_t oct = (r.ix < 0.0f ? 1u : 0u) | (r.iy < 0.0f ? 2u : 0u) | (r.iz < 0.0f ? 4u : 0u);
     r.octinv4 = (7u ^ oct) * 0x01010101u;
 }
 
@@ -164,12 +165,13 @@ RTC_HD void bvh_test_tri(const BvhView& b, const Ray& ray, uint32_t ti, BvhTrav&
     }
 }
 
-// One iteration: pop the nearest pending child (or a postponed triangle group), test its children, test the
-// triangles of the leaves that were hit, pop the stack when the group is used up. Returns true when the ray is done.
-// nodes / tests count what the STATS build reports (80-byte node records, 48-byte triangle records fetched).
+// One iteration in two halves, so that the kernel can put the triangle tests of a whole warp into one pool between
+// them. bvh_step_nodes: pop the nearest pending child (or a postponed triangle group) and test its children; returns
+// the triangle group {tri_base, one bit per triangle of the leaves that were hit}. bvh_step_pop: take the next group
+// off the stack when the current one is used up; returns true when the ray is done.
+// nodes counts what the STATS build reports (80-byte node records fetched).
 template <bool STATS>
-RTC_HD bool bvh_step(const BvhView& b, const BvhRay& r, const Ray& ray, BvhTrav& s, uint2* stack, uint32_t stride,
-                     uint32_t& nodes, uint32_t& tests)
+RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2* stack, uint32_t stride, uint32_t& nodes)
 {
     uint2 tg;
     if (s.ng.y > 0x00FFFFFFu) {
@@ -185,18 +187,31 @@ RTC_HD bool bvh_step(const BvhView& b, const BvhRay& r, const Ray& ray, BvhTrav&
         tg = s.ng;
         s.ng = make_uint2(0u, 0u);
     }
-    while (tg.y != 0u) {
-        const uint32_t rel = 31u - bvh_clz(tg.y);
-        tg.y &= ~(1u << rel);
-        if (STATS) tests += 1u;
-        bvh_test_tri(b, ray, tg.x + rel, s);
-    }
+    return tg;
+}
+RTC_HD bool bvh_step_pop(BvhTrav& s, const uint2* stack, uint32_t stride)
+{
     if (s.ng.y <= 0x00FFFFFFu) {
         if (s.sp == 0u) return true;
         s.sp -= 1u;
         s.ng = stack[s.sp * stride];
     }
     return false;
+}
+
+// The whole iteration for one ray on its own (the host-side checker, tests/native/bvh_check.cu).
+template <bool STATS>
+RTC_HD bool bvh_step(const BvhView& b, const BvhRay& r, const Ray& ray, BvhTrav& s, uint2* stack, uint32_t stride,
+                     uint32_t& nodes, uint32_t& tests)
+{
+    uint2 tg = bvh_step_nodes<STATS>(b, r, s, stack, stride, nodes);
+    while (tg.y != 0u) {
+        const uint32_t rel = 31u - bvh_clz(tg.y);
+        tg.y &= ~(1u << rel);
+        if (STATS) tests += 1u;
+        bvh_test_tri(b, ray, tg.x + rel, s);
+    }
+    return bvh_step_pop(s, stack, stride);
 }
 
 }  // namespace rtc

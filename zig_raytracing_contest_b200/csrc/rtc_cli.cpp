@@ -6,7 +6,8 @@
 // (Loaded / Preprocessed / Compiled / Rendered / Saved / Done, src/main.zig:106-142). Everything it calls is
 // the C ABI of include/rtc.h; there is no CPU render fallback.
 //
-// Options beyond the reference's, all optional: --device N, --seed N, --mode path|primary, --math exact|fast.
+// Options beyond the reference's, all optional: --device N, --seed N, --mode path|primary, --math exact|fast,
+// --accel grid|bvh, --gpus N (one process, N devices, one rtc_render call), --shard strips|samples.
 #include "../../include/rtc.h"
 
 #include <chrono>
@@ -22,9 +23,8 @@ namespace {
 using Clock = std::chrono::steady_clock;
 
 // std.fmt.fmtDuration-style: the largest unit that keeps the value >= 1, three decimals.
-std::string since(Clock::time_point t0)
+std::string fmt_ns(double ns)
 {
-    const double ns = (double)std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now() - t0).count();
     char buf[64];
     if (ns >= 60e9) snprintf(buf, sizeof buf, "%dm%.3fs", (int)(ns / 60e9), (ns - 60e9 * (int)(ns / 60e9)) / 1e9);
     else if (ns >= 1e9) snprintf(buf, sizeof buf, "%.3fs", ns / 1e9);
@@ -33,6 +33,10 @@ std::string since(Clock::time_point t0)
     else snprintf(buf, sizeof buf, "%.0fns", ns);
     return buf;
 }
+std::string since(Clock::time_point t0)
+{
+    return fmt_ns((double)std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now() - t0).count());
+}
 
 struct Args {
     std::string in = "input.gltf", out = "output.png", camera;
@@ -40,7 +44,8 @@ struct Args {
     uint32_t width = 0, height = 0;            // 0 = not given (?u16 = null)
     int device = -1;
     uint64_t seed = 0;
-    uint32_t mode = RTC_MODE_PATH, math = RTC_MATH_EXACT;
+    uint32_t mode = RTC_MODE_PATH, math = RTC_MATH_EXACT, accel = RTC_ACCEL_GRID, shard = RTC_SHARD_STRIPS;
+    int gpus = 1;
 };
 
 bool parse_u(const std::string& v, uint64_t max, uint64_t* out)
@@ -66,7 +71,7 @@ bool parse_args(int argc, char** argv, Args* a)
         const size_t eq = name.find('=');
         bool has_value = eq != std::string::npos;
         if (has_value) { value = name.substr(eq + 1); name = name.substr(0, eq); }
-        static const char* known[] = { "in", "out", "camera", "width", "height", "device", "seed", "mode", "math" };
+        static const char* known[] = { "in", "out", "camera", "width", "height", "device", "seed", "mode", "math", "accel", "gpus", "shard" };
         bool is_known = false;
         for (const char* k : known) is_known = is_known || name == k;
         if (!is_known) { fprintf(stderr, "Unknown command line option: %s\n", name.c_str()); ok = false; continue; }
@@ -86,6 +91,13 @@ bool parse_args(int argc, char** argv, Args* a)
         else if (name == "mode") {
             if (value == "path") a->mode = RTC_MODE_PATH; else if (value == "primary") a->mode = RTC_MODE_PRIMARY;
             else { fprintf(stderr, "Invalid value '%s' for option mode\n", value.c_str()); ok = false; }
+        } else if (name == "gpus") { if (!parse_u(value, RTC_MAX_GPUS, &u) || u == 0) { fprintf(stderr, "Invalid value '%s' for option gpus\n", value.c_str()); ok = false; continue; } a->gpus = (int)u; }
+        else if (name == "shard") {
+            if (value == "strips") a->shard = RTC_SHARD_STRIPS; else if (value == "samples") a->shard = RTC_SHARD_SAMPLES;
+            else { fprintf(stderr, "Invalid value '%s' for option shard\n", value.c_str()); ok = false; }
+        } else if (name == "accel") {
+            if (value == "grid") a->accel = RTC_ACCEL_GRID; else if (value == "bvh") a->accel = RTC_ACCEL_BVH;
+            else { fprintf(stderr, "Invalid value '%s' for option accel\n", value.c_str()); ok = false; }
         } else if (name == "math") {
             if (value == "exact") a->math = RTC_MATH_EXACT; else if (value == "fast") a->math = RTC_MATH_FAST;
             else { fprintf(stderr, "Invalid value '%s' for option math\n", value.c_str()); ok = false; }
@@ -135,8 +147,16 @@ int main(int argc, char** argv)
                                        args.device, &scene, &camera, &bi) != RTC_OK)
             return die(args.in.c_str());
         fprintf(stderr, "info: Pixels count: %u\n", camera.w * camera.h);
-        fprintf(stderr, "info: Loaded, preprocessed and compiled in %s (device: triangle assembly %.3fms, grid build %.3fms)\n", since(t).c_str(),
-                (double)bi.assemble_ms, (double)bi.device_ms);
+        // The reference's three phase lines (src/main.zig:106,113,119), in its order. The call above fuses the phases, so
+        // the brackets are its own clocks: everything that is not a device kernel (files, JSON, image decode, uploads)
+        // is the load; triangle assembly + texel linearisation on the device is the preprocessing; the grid build +
+        // bake kernels are the compile.
+        const double fused_ms = std::chrono::duration<double, std::milli>(Clock::now() - t).count();
+        const double pre_ms = (double)bi.assemble_ms, comp_ms = (double)bi.device_ms;
+        const double load_ms = fused_ms > pre_ms + comp_ms ? fused_ms - pre_ms - comp_ms : 0.0;
+        fprintf(stderr, "info: Loaded in %s\n", fmt_ns(load_ms * 1e6).c_str());
+        fprintf(stderr, "info: Preprocessed in %s\n", fmt_ns(pre_ms * 1e6).c_str());
+        fprintf(stderr, "info: Compiled in %s\n", fmt_ns(comp_ms * 1e6).c_str());
     } else {
         // RTC_HOST_LOAD=1: stage1 on host threads, the grid built and baked on the device from the uploaded soup.
         // RTC_HOST_BUILD=1: stage2 on a host thread too, the baked arrays uploaded. Same scene bit for bit.
@@ -179,7 +199,8 @@ int main(int argc, char** argv)
     rtc_params prm;
     memset(&prm, 0, sizeof prm);
     prm.num_samples = config.num_samples; prm.max_bounce = config.max_bounce;
-    prm.mode = args.mode; prm.seed = args.seed; prm.accel = RTC_ACCEL_GRID; prm.math = args.math;
+    prm.mode = args.mode; prm.seed = args.seed; prm.accel = args.accel; prm.math = args.math;
+    prm.num_gpus = args.gpus > 1 ? args.gpus : 0; prm.shard = args.shard;      // still ONE blocking call (src/main.zig:126)
     rtc_stats stats;
     memset(&stats, 0, sizeof stats);
     rtc_aux aux;

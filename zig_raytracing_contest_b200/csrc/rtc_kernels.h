@@ -32,6 +32,12 @@ struct LaunchCfg {
 
 struct BvhView;
 
+// the accumulators of the devices of an in-process multi-GPU render, as seen from one of them (peer pointers)
+struct PeerAccums {
+    const float4* p[16];
+    uint32_t n;
+};
+
 struct PrimaryOut {
     uint32_t* hit_id;      // num_pixels, source-triangle id or 0xFFFFFFFF (may be null)
     float* hit_tuv;        // 3*num_pixels (may be null)
@@ -51,6 +57,15 @@ struct PrimaryOut {
     /* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242).                                      */ \
     cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t total_samples,      \
                                uint8_t* rgb, float* radiance, cudaStream_t stream);                   \
+    /* sample sharding: sum of the devices' accumulators over peer memory + resolve, pixels           */ \
+    /* [first, first+count) (in-process); rgb-only packing and the resolve from it (rtc_comm)         */ \
+    cudaError_t launch_combine_resolve(const PeerAccums& pa, uint32_t first, uint32_t count,          \
+                                       uint32_t total_samples, uint8_t* rgb, float* radiance,         \
+                                       cudaStream_t stream);                                          \
+    cudaError_t launch_pack_rgb(const float4* accum, uint32_t num_pixels, float* rgb3,                \
+                                cudaStream_t stream);                                                 \
+    cudaError_t launch_resolve3(const float* sum3, uint32_t num_pixels, uint32_t total_samples,       \
+                                uint8_t* rgb, cudaStream_t stream);                                   \
     }
 
 RTC_DECLARE_LAUNCHERS(exact)

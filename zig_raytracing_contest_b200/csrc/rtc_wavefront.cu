@@ -84,7 +84,10 @@ __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const
     // streaming (evict-first) accesses keep them from pushing the scene out of L2.
     __stcs(q.a0 + i, make_float4(e.r.o.x, e.r.o.y, e.r.o.z, __uint_as_float(e.slot)));
     __stcs(q.a1 + i, make_float4(e.r.d.x, e.r.d.y, e.r.d.z, __uint_as_float(e.top)));
-    if (BVH) return;                                    // RTC_ACCEL_BVH: no iterator state, 32 B / ray
+    if (BVH) {                                          // RTC_ACCEL_BVH: 1/d and the octant word instead of the iterator, 48 B / ray
+        __stcs(q.a2 + i, make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec)));
+        return;
+    }
     __stcs(q.a2 + i, make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec)));
     __stcs(q.a3 + i, make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.c)));
 }
@@ -102,11 +105,17 @@ __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, b
 }
 
 // What a new ray needs before it is queued. Grid: Grid.traceRay's iterator (a ray that misses the grid's box is a
-// miss right away, stage3.zig:159). BVH: nothing — the root's slab test plays that part in k_trace_bvh.
+// miss right away, stage3.zig:159). BVH: 1/d and the octant word (the root's slab test plays the part of the grid's
+// box test in k_trace_bvh).
 template <bool BVH>
 __device__ __forceinline__ bool ray_setup(const DevScene& sc, const Ray& r, QueuedRay& q)
 {
-    if (BVH) { q.r = r; return true; }
+    if (BVH) {
+        BvhRay br;
+        bvh_ray_init(br, r.o, r.d);                     // three divisions, here at full lanes instead of at k_trace_bvh's refill
+        q.r = r; q.tx = br.ix; q.ty = br.iy; q.tz = br.iz; q.ec = br.octinv4;
+        return true;
+    }
     return queue_setup(sc, r, q);
 }
 
@@ -326,24 +335,40 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 
 // ---------------------------------------------------------------------------------------------------------
 // k_trace_bvh: Scene.traceRay (src/stage3.zig:152-186) over a ray queue with the 8-wide BVH of rtc_bvh.cuh in
-// place of the grid (RTC_ACCEL_BVH). Persistent warps with the same per-lane refill as k_trace; every lane walks
-// its own ray: one bvh_step = pop the nearest pending child, one 80-byte node (five 128-bit loads), eight slab
-// tests on quantised boxes, the triangles of the leaves that were hit (48-byte records, three 128-bit loads) with
-// the reference's Triangle.rayIntersection. The traversal stack lives in shared memory for the first kBvhSmemStack
-// entries of every lane (interleaved by lane: conflict-free) and in local memory beyond.
+// place of the grid (RTC_ACCEL_BVH). Persistent warps with the same per-lane refill as k_trace. One round:
+//   A  every live lane pops the nearest pending child of its own ray and tests that node's eight quantised boxes
+//      (one 80-byte node = five 128-bit loads; the lanes of a warp run this part converged);
+//   B  the triangles of the leaves that were hit — a few per lane, none for most — are POOLED over the warp and
+//      dealt out one (ray, triangle) pair per lane per pass (48-byte records, three 128-bit loads, the reference's
+//      Triangle.rayIntersection). Tested per lane they ran at 3.5 of 32 lanes (profiles/r2b_*). Winner per ray =
+//      atomicMin on (t bits << 32 | source id) in shared memory: smallest t > 0, smaller source id on exact ties;
+//   C  owners fold their winner in (strictly nearer, or equal and smaller source id) and pop their stack.
+// The traversal stack is per lane, in local memory (L1-resident: a few entries deep in practice).
 #ifndef RTC_BVH_MINB
-#define RTC_BVH_MINB 3
+#define RTC_BVH_MINB 4
 #endif
 #ifndef RTC_BVH_REFILL
-#define RTC_BVH_REFILL 1
+#define RTC_BVH_REFILL 4
 #endif
 static constexpr uint32_t kBvhRefillMin = RTC_BVH_REFILL;     // refill when at least this many lanes of the warp are idle
+static constexpr uint32_t kBvhPool = 32u * 24u;               // a lane's triangle group holds at most 24 triangles
+
+struct BvhShared {
+    float4 ro[32];                      // per lane: ray origin
+    float4 rd[32];                      // per lane: ray direction
+    unsigned long long best[32];        // per lane: min over this round's (t bits << 32 | source id)
+    uint32_t win[32];                   // per lane: BVH index of the triangle holding best
+    uint32_t base[32];                  // per lane: tri_base of its triangle group
+    unsigned short pool[kBvhPool];      // (owner lane << 8 | triangle offset) per pooled pair
+};
 
 template <bool STATS>
 __global__ void __launch_bounds__(kTraceThreads, RTC_BVH_MINB)
 k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ count_ptr, uint32_t* __restrict__ head_ptr,
             uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
+    __shared__ BvhShared s_ws[kTraceWarps];
+    BvhShared& ws = s_ws[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t n = __ldg(count_ptr);
@@ -351,12 +376,12 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
     uint32_t next = 0, end = 0;
     bool exhausted = false, alive = false;
     uint32_t qi = 0;
-    Ray ray; BvhRay br; BvhTrav s;
-    ray.o = ray.d = splat(0.0f);
-    bvh_ray_init(br, ray.o, ray.d);
+    BvhRay br; BvhTrav s;
+    br.ox = br.oy = br.oz = 0.0f; br.ix = br.iy = br.iz = 1.0f; br.octinv4 = 0u;
     bvh_trav_begin(s);
     uint2 stack[kBvhStack];
     for (;;) {
+        // ---- refill: idle lanes take the next rays of the queue ----
         const uint32_t idle = __ballot_sync(kFull, !alive);
         if (idle != 0u && !exhausted && ((uint32_t)__popc(idle) >= kBvhRefillMin || idle == kFull)) {
             if (next == end) {
@@ -370,9 +395,10 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
             const uint32_t take = want < avail ? want : avail;
             if (!alive && (uint32_t)__popc(idle & lt_mask) < take) {
                 qi = next + __popc(idle & lt_mask);
-                const float4 a0 = __ldcs(q.a0 + qi), a1 = __ldcs(q.a1 + qi);
-                ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
-                bvh_ray_init(br, ray.o, ray.d);
+                const float4 a0 = __ldcs(q.a0 + qi), a1 = __ldcs(q.a1 + qi), a2 = __ldcs(q.a2 + qi);
+                ws.ro[lane] = a0; ws.rd[lane] = a1;
+                br.ox = a0.x; br.oy = a0.y; br.oz = a0.z; br.ix = a2.x; br.iy = a2.y; br.iz = a2.z;
+                br.octinv4 = __float_as_uint(a2.w);
                 bvh_trav_begin(s);
                 alive = true;
             }
@@ -382,7 +408,65 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
             if (exhausted) break;
             continue;
         }
-        if (alive && bvh_step<STATS>(bv, br, ray, s, stack, 1u, cn.cells, cn.tris)) {
+        // ---- A: one node per live lane ----
+        uint2 tg = make_uint2(0u, 0u);
+        if (alive) tg = bvh_step_nodes<STATS>(bv, br, s, stack, 1u, cn.cells);
+        // ---- B: pooled triangle tests ----
+        const uint32_t cnt = __popc(tg.y);
+        if (STATS) cn.tris += cnt;
+        if (__ballot_sync(kFull, cnt != 0u) != 0u) {
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, d); if (lane >= (uint32_t)d) incl += v; }
+            const uint32_t total = __shfl_sync(kFull, incl, 31);
+            if (cnt != 0u) {
+                uint32_t o = incl - cnt, m = tg.y;
+                ws.base[lane] = tg.x;
+                ws.best[lane] = ~0ull;
+                do {
+                    const uint32_t b = 31u - (uint32_t)__clz((int)m);
+                    m &= ~(1u << b);
+                    ws.pool[o++] = (unsigned short)((lane << 8) | b);
+                } while (m != 0u);
+            }
+            __syncwarp();
+            for (uint32_t base = 0; base < total; base += 32u) {
+                const uint32_t j = base + lane;
+                unsigned long long key = ~0ull;
+                uint32_t owner = 0u, ti = 0u;
+                if (j < total) {
+                    const uint32_t e = ws.pool[j];
+                    owner = e >> 8;
+                    ti = ws.base[owner] + (e & 0xFFu);
+                    const float4* p = bv.tris + 3u * (size_t)ti;
+                    const float4 a = __ldg(p), e1 = __ldg(p + 1), e2 = __ldg(p + 2);
+                    const float4 o4 = ws.ro[owner], d4 = ws.rd[owner];
+                    Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
+                    float t, u, v;
+                    if (tri_ray(mk(a.x, a.y, a.z), mk(e1.x, e1.y, e1.z), mk(e2.x, e2.y, e2.z), r, t, u, v) && t > 0.0f) {
+                        key = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(a.w);
+                        atomicMin(&ws.best[owner], key);
+                    }
+                }
+                __syncwarp();
+                if (key != ~0ull && ws.best[owner] == key) ws.win[owner] = ti;     // source ids are unique: one winner
+                __syncwarp();
+            }
+            // ---- C (first half): owners fold the round's winner in ----
+            if (cnt != 0u) {
+                const unsigned long long k = ws.best[lane];
+                if (k != ~0ull) {
+                    const float t = __uint_as_float((uint32_t)(k >> 32));
+                    bool take = s.best_t > t;
+                    if (!take && s.best_t == t && s.best_tri != kMiss)
+                        take = (uint32_t)k < __float_as_uint(__ldg(bv.tris + 3u * (size_t)s.best_tri).w);
+                    if (take) { s.best_t = t; s.best_tri = ws.win[lane]; }
+                }
+            }
+            __syncwarp();
+        }
+        // ---- C (second half): next group, or the ray is done ----
+        if (alive && bvh_step_pop(s, stack, 1u)) {
             __stcs(hits + qi, make_uint2(__float_as_uint(s.best_t), s.best_tri));
             alive = false;
         }
@@ -555,6 +639,55 @@ k_resolve(const float4* __restrict__ accum, uint32_t num_pixels, uint32_t total_
     }
 }
 
+// Sample sharding inside one process (rtc_params.num_gpus > 1, RTC_SHARD_SAMPLES): the reduce of the per-device
+// accumulators and the resolve in ONE kernel over NVLink peer memory. Device g runs it on ITS slice of the pixels and
+// reads that slice of every device's accumulator directly (P2P loads, 16 B per pixel and peer), adds them in device
+// order — a fixed order, so the frame does not depend on timing — scales by 1/S and writes RGB8 (+ radiance): a
+// reduce-scatter fused with stage3.zig:242, after which every device copies its own slice to the host frame.
+__global__ void __launch_bounds__(kThreads)
+k_combine_resolve(const PeerAccums pa, uint32_t first, uint32_t count, uint32_t total_samples,
+                  uint8_t* __restrict__ rgb, float* __restrict__ radiance)
+{
+    const uint32_t k = blockIdx.x * kThreads + threadIdx.x;
+    if (k >= count) return;
+    const uint32_t i = first + k;
+    float4 a = pa.p[0][i];
+    for (uint32_t j = 1; j < pa.n; ++j) {
+        const float4 b = __ldcs(pa.p[j] + i);
+        a.x = a.x + b.x; a.y = a.y + b.y; a.z = a.z + b.z;
+    }
+    const float inv = 1.0f / (float)total_samples;
+    const float r = a.x * inv, g = a.y * inv, b = a.z * inv;
+    if (radiance) { radiance[3 * (size_t)i] = r; radiance[3 * (size_t)i + 1] = g; radiance[3 * (size_t)i + 2] = b; }
+    if (rgb) {
+        rgb[3 * (size_t)i] = (uint8_t)to_rgb8(r);
+        rgb[3 * (size_t)i + 1] = (uint8_t)to_rgb8(g);
+        rgb[3 * (size_t)i + 2] = (uint8_t)to_rgb8(b);
+    }
+}
+
+// One process per GPU (rtc_render_sharded, RTC_SHARD_SAMPLES): the accumulators travel as rgb only — the sample count
+// in .w is the same on every rank's frame and a quarter of the bytes. k_pack_rgb: float4 -> 3 floats; k_resolve3: the
+// resolve from the summed 3-float rows.
+__global__ void __launch_bounds__(kThreads)
+k_pack_rgb(const float4* __restrict__ accum, uint32_t num_pixels, float* __restrict__ rgb3)
+{
+    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= num_pixels) return;
+    const float4 a = accum[i];
+    rgb3[3 * (size_t)i] = a.x; rgb3[3 * (size_t)i + 1] = a.y; rgb3[3 * (size_t)i + 2] = a.z;
+}
+__global__ void __launch_bounds__(kThreads)
+k_resolve3(const float* __restrict__ sum3, uint32_t num_pixels, uint32_t total_samples, uint8_t* __restrict__ rgb)
+{
+    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= num_pixels) return;
+    const float inv = 1.0f / (float)total_samples;
+    rgb[3 * (size_t)i] = (uint8_t)to_rgb8(sum3[3 * (size_t)i] * inv);
+    rgb[3 * (size_t)i + 1] = (uint8_t)to_rgb8(sum3[3 * (size_t)i + 1] * inv);
+    rgb[3 * (size_t)i + 2] = (uint8_t)to_rgb8(sum3[3 * (size_t)i + 2] * inv);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 template <typename K>
 static int blocks_per_sm(K kernel, int threads, size_t smem)
@@ -681,6 +814,26 @@ cudaError_t launch_resolve(const float4* accum, uint32_t num_pixels, uint32_t to
 {
     if (num_pixels == 0) return cudaSuccess;
     k_resolve<<<(num_pixels + kThreads - 1) / kThreads, kThreads, 0, stream>>>(accum, num_pixels, total_samples, rgb, radiance);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_combine_resolve(const PeerAccums& pa, uint32_t first, uint32_t count, uint32_t total_samples,
+                                   uint8_t* rgb, float* radiance, cudaStream_t stream)
+{
+    if (count == 0) return cudaSuccess;
+    k_combine_resolve<<<(count + kThreads - 1) / kThreads, kThreads, 0, stream>>>(pa, first, count, total_samples, rgb, radiance);
+    return cudaGetLastError();
+}
+cudaError_t launch_pack_rgb(const float4* accum, uint32_t num_pixels, float* rgb3, cudaStream_t stream)
+{
+    if (num_pixels == 0) return cudaSuccess;
+    k_pack_rgb<<<(num_pixels + kThreads - 1) / kThreads, kThreads, 0, stream>>>(accum, num_pixels, rgb3);
+    return cudaGetLastError();
+}
+cudaError_t launch_resolve3(const float* sum3, uint32_t num_pixels, uint32_t total_samples, uint8_t* rgb, cudaStream_t stream)
+{
+    if (num_pixels == 0) return cudaSuccess;
+    k_resolve3<<<(num_pixels + kThreads - 1) / kThreads, kThreads, 0, stream>>>(sum3, num_pixels, total_samples, rgb);
     return cudaGetLastError();
 }
 

@@ -50,6 +50,13 @@ def lib():
     L.rtc_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
     L.rtc_scene_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.BvhInfo)]
+    L.rtc_scene_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.rtc_comm_unique_id.argtypes = [C.c_void_p]
+    L.rtc_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    L.rtc_comm_destroy.argtypes = [C.c_void_p]
+    L.rtc_comm_destroy.restype = None
+    L.rtc_render_sharded.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Params), C.c_void_p,
+                                     C.POINTER(abi.Aux)]
     L.rtc_geometry_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(abi.Geometry)]
     L.rtc_geometry_build_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int,
                                             C.POINTER(abi.Geometry)]
@@ -248,7 +255,7 @@ def make_scene_desc(geometry, materials):
 
 def make_params(num_samples=3, max_bounce=4, mode=abi.RTC_MODE_PATH, seed=0, sample_offset=0,
                 total_samples=0, math=abi.RTC_MATH_EXACT, tile_rank=0, tile_world=0, collect_stats=False,
-                tile_rows=0, accel=abi.RTC_ACCEL_GRID):
+                tile_rows=0, accel=abi.RTC_ACCEL_GRID, num_gpus=0, shard=abi.RTC_SHARD_STRIPS):
     """main.Config's num_samples / max_bounce (src/main.zig:56-61; config.json defaults 3 and 4)."""
     p = abi.Params()
     p.num_samples, p.max_bounce, p.mode, p.seed = num_samples, max_bounce, mode, seed
@@ -256,7 +263,35 @@ def make_params(num_samples=3, max_bounce=4, mode=abi.RTC_MODE_PATH, seed=0, sam
     p.accel, p.math = accel, math
     p.tile_rank, p.tile_world, p.collect_stats = tile_rank, tile_world, 1 if collect_stats else 0
     p.tile_rows = tile_rows
+    p.num_gpus, p.shard = num_gpus, shard
     return p
+
+
+# ---- one process per GPU: the library's own NCCL communicator ---------------------------------------------
+def comm_unique_id():
+    """rank 0: the 128-byte id every rank passes to Comm (hand it over with MPI / torch.distributed / a file)."""
+    buf = (C.c_uint8 * abi.RTC_COMM_ID_BYTES)()
+    _check(lib().rtc_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Comm:
+    """rtc_comm: one rank of a frame sharded over processes (collective create: ncclCommInitRank)."""
+
+    def __init__(self, unique_id, rank, world, device=-1):
+        if len(unique_id) != abi.RTC_COMM_ID_BYTES:
+            raise ValueError("unique_id must be %d bytes" % abi.RTC_COMM_ID_BYTES)
+        self._h = C.c_void_p()
+        self.rank, self.world = int(rank), int(world)
+        buf = (C.c_uint8 * abi.RTC_COMM_ID_BYTES).from_buffer_copy(unique_id)
+        _check(lib().rtc_comm_create(buf, self.rank, self.world, int(device), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().rtc_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
 
 
 # ---- stage3: Scene ---------------------------------------------------------------------------------
@@ -311,9 +346,10 @@ class Scene:
 
     __del__ = close
 
-    def render(self, camera, params, img=None, want_radiance=False, want_hits=False, want_stats=False):
+    def render(self, camera, params, img=None, want_radiance=False, want_hits=False, want_stats=False, instrumented=True):
         """Blocking render into img ([h,w,3] uint8, row 0 = top). Returns a dict with rgb and the
-        optional aux outputs."""
+        optional aux outputs. want_stats runs the instrumented kernels (cell / triangle-test counters) unless
+        instrumented=False (rays, paths, hits and the timings only)."""
         w, h = int(camera.w), int(camera.h)
         if img is None:
             img = np.zeros((h, w, 3), np.uint8)
@@ -332,12 +368,41 @@ class Scene:
         st = abi.Stats()
         if want_stats:
             aux.stats = C.pointer(st)
-            params = abi.Params.from_buffer_copy(params)
-            params.collect_stats = 1                 # instrumented kernels: cells / triangle-test counters
+            if instrumented:
+                params = abi.Params.from_buffer_copy(params)
+                params.collect_stats = 1             # instrumented kernels: cells / triangle-test counters
         _check(lib().rtc_render(self._h, C.byref(camera), C.byref(params), img.ctypes.data, C.byref(aux)))
         if want_stats:
             out["stats"] = st.as_dict()
         return out
+
+    def render_sharded(self, comm, camera, params, img=None, want_stats=False, to_host=True):
+        """rtc_render_sharded: this rank's share of one frame; the frame arrives on rank 0 (in `img` when to_host,
+        else it stays in rank 0's device memory). comm=None: this process alone. Returns dict(rgb?, stats?)."""
+        w, h = int(camera.w), int(camera.h)
+        rank = comm.rank if comm is not None else 0
+        out = {}
+        ptr = None
+        if to_host and rank == 0:
+            if img is None:
+                img = np.zeros((h, w, 3), np.uint8)
+            if img.shape != (h, w, 3) or img.dtype != np.uint8 or not img.flags.c_contiguous:
+                raise ValueError("img must be a contiguous [h,w,3] uint8 array")
+            out["rgb"] = img
+            ptr = img.ctypes.data
+        aux = abi.Aux()
+        st = abi.Stats()
+        if want_stats:
+            aux.stats = C.pointer(st)
+        _check(lib().rtc_render_sharded(self._h, comm._h if comm is not None else None, C.byref(camera), C.byref(params),
+                                        C.c_void_p(ptr), C.byref(aux)))
+        if want_stats:
+            out["stats"] = st.as_dict()
+        return out
+
+    def set_stream(self, stream_ptr=None):
+        """Every later call on this scene launches on this cudaStream_t (None: back to the scene's own stream)."""
+        _check(lib().rtc_scene_set_stream(self._h, C.c_void_p(stream_ptr or 0)))
 
     def render_accumulate(self, camera, params, d_accum_ptr, stream_ptr=None):
         """Adds params.num_samples samples per pixel into a device float4 accumulator (async)."""
