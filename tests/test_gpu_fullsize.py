@@ -91,3 +91,53 @@ def test_cfg4_scene_4k_bands(orc):
     # same samples added in the same order into one accumulator: bit-identical to the single call
     assert np.array_equal(_bits(rad.cpu().numpy().reshape(cam.h, cam.w, 3)), _bits(g["radiance"]))
     scene.close()
+
+
+def test_cfg4_5M_triangles_4k_bands_grid_and_bvh(orc):
+    """configs[3] on the scene its bench lines are quoted on: 5 000 000 source triangles, 3840x2160, camera inside
+    the grid. The scene is built on the device from the soup; the oracle bakes the same soup on the CPU (8 s). Grid:
+    radiance bit-exact on two bands of 2 rows at 4 spp, primary hit ids / t,u,v bit-exact on the same bands. BVH
+    (RTC_ACCEL_BVH): primary hit ids equal except enumerated near-ties (each one classified), t,u,v bit-exact on
+    equal ids; path radiance bit-identical on >= 99.9 %% of the band pixels."""
+    from test_gpu_bvh import classify
+    spec = scenes.terrain(5_000_000)
+    scene = rtc.Scene.from_soup(spec.positions, spec.tri_data, (128, 128, 128), spec.materials, device=0)
+    geo = orc.Geometry(spec.positions, spec.tri_data, (128, 128, 128))
+    assert int(scene.build_info.num_tris) == geo.tri_pos.shape[0] and int(scene.build_info.num_src_tris) == 5_000_000
+    desc, keep = rtc.make_scene_desc(geo, spec.materials)
+    scene.desc = desc
+    cam = spec.camera(height=2160)
+    assert (cam.w, cam.h) == (3840, 2160)
+    info = scene.build_bvh()
+    assert info["num_tris"] == 5_000_000 and info["depth"] < 40
+    bands = (700, 1500)
+    prm = rtc.make_params(num_samples=4, max_bounce=4, seed=1)
+    g = scene.render(cam, prm, want_radiance=True, want_stats=True, instrumented=False)
+    b = scene.render(cam, rtc.make_params(num_samples=4, max_bounce=4, seed=1, accel=abi.RTC_ACCEL_BVH), want_radiance=True,
+                     want_stats=True, instrumented=False)
+    assert g["stats"]["paths"] == b["stats"]["paths"] == 3840 * 2160 * 4
+    assert abs(b["stats"]["rays"] - g["stats"]["rays"]) <= 1e-4 * g["stats"]["rays"]
+    p1 = rtc.make_params(mode=abi.RTC_MODE_PRIMARY)
+    gp = scene.render(cam, p1, want_hits=True)
+    bp = scene.render(cam, rtc.make_params(mode=abi.RTC_MODE_PRIMARY, accel=abi.RTC_ACCEL_BVH), want_hits=True)
+    exact_px = total_px = 0
+    for y0 in bands:
+        rows = slice(y0, y0 + 2)
+        o = orc.render(desc, cam, prm, rows=(y0, y0 + 2), want_radiance=True)
+        assert np.array_equal(_bits(g["radiance"][rows]), _bits(o["radiance"][rows]))
+        same = (_bits(b["radiance"][rows]) == _bits(o["radiance"][rows])).all(axis=-1)
+        exact_px += int(same.sum()); total_px += same.size
+        op = orc.render(desc, cam, p1, rows=(y0, y0 + 2), want_hits=True)
+        assert np.array_equal(gp["hit_id"][rows], op["hit_id"][rows])
+        assert np.array_equal(_bits(gp["hit_tuv"][rows]), _bits(op["hit_tuv"][rows]))
+        eq = bp["hit_id"][rows] == op["hit_id"][rows]
+        assert np.array_equal(_bits(bp["hit_tuv"][rows])[eq], _bits(op["hit_tuv"][rows])[eq])
+        sub_g = {"hit_id": np.full_like(bp["hit_id"], abi.MISS_ID), "hit_tuv": bp["hit_tuv"]}
+        sub_o = {"hit_id": np.full_like(op["hit_id"], abi.MISS_ID), "hit_tuv": op["hit_tuv"]}
+        sub_g["hit_id"][rows] = bp["hit_id"][rows]; sub_o["hit_id"][rows] = op["hit_id"][rows]
+        c = classify(orc, scene, geo, cam, sub_g, sub_o)
+        print("cfg4 5M band", y0, "bvh vs oracle:", c, "of", eq.size)
+        assert c["unexplained"] == 0 and c["total"] <= 1e-3 * eq.size, c
+    print("cfg4 5M bvh path radiance bit-identical pixels: %d / %d" % (exact_px, total_px))
+    assert exact_px >= 0.999 * total_px
+    scene.close()

@@ -82,11 +82,19 @@ def _worker(rank, world, port, out_dir):
     for a, b in shard.strips_of(rank, world, cam.h, 4):
         mine[a:b] = torch.from_numpy(oracle.render(desc, cam, full_prm, num_threads=1, rows=(a, b))["rgb"][a:b].copy())
     frame2 = shard.gather_strips(mine, 4, dst=0)
+    # a NON-CONTIGUOUS frame whose strips tile it exactly (27 rows = 3 strips of 9): reshape of a strided tensor copies,
+    # so the gathered strips must still land in the frame that is returned
+    strided = torch.zeros(cam.h, cam.w * 2, 3, dtype=torch.uint8)[:, ::2]
+    assert not strided.is_contiguous()
+    for a, b in shard.strips_of(rank, world, cam.h, 9):
+        strided[a:b] = torch.from_numpy(oracle.render(desc, cam, full_prm, num_threads=1, rows=(a, b))["rgb"][a:b].copy())
+    frame3 = shard.gather_strips(strided, 9, dst=0)
     if rank == 0:
         ref = oracle.render(desc, cam, full_prm, num_threads=1)
         np.save(os.path.join(out_dir, "acc.npy"), acc.numpy())
         np.save(os.path.join(out_dir, "frame.npy"), frame.numpy())
         np.save(os.path.join(out_dir, "frame2.npy"), frame2.numpy())
+        np.save(os.path.join(out_dir, "frame3.npy"), frame3.numpy())
         np.save(os.path.join(out_dir, "ref_rad.npy"), ref["radiance"])
         np.save(os.path.join(out_dir, "ref_rgb.npy"), ref["rgb"])
     dist.barrier()
@@ -102,3 +110,4 @@ def test_two_ranks_reproduce_the_single_frame(tmp_path, orc):
     np.testing.assert_allclose(acc[:, :3] / 6.0, ref_rad, rtol=3e-6, atol=1e-7)   # fp32 sum reordering only
     assert np.array_equal(np.load(tmp_path / "frame.npy"), np.load(tmp_path / "ref_rgb.npy"))
     assert np.array_equal(np.load(tmp_path / "frame2.npy"), np.load(tmp_path / "ref_rgb.npy"))
+    assert np.array_equal(np.load(tmp_path / "frame3.npy"), np.load(tmp_path / "ref_rgb.npy"))

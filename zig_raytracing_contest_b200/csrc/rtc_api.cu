@@ -230,7 +230,6 @@ int rtc_scene_upload_materials_(rtc_scene* s, const rtc_material* materials, uin
 
 int rtc_scene_finish_(rtc_scene* s)
 {
-    s->dev.tri_mul = 1u;
     if (int rc = s->alloc(&s->counters, (size_t)rtc::CNT_N)) return rc;
     if (int rc = s->alloc(&s->work, (size_t)4)) return rc;
     CU(cudaMemset(s->counters, 0, rtc::CNT_N * sizeof(unsigned long long)));
@@ -449,12 +448,10 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
     cfg.cache = &s->cache;
     uint32_t launches = 0;
     const rtc::BvhView* bvh = nullptr;
-    rtc::DevScene dev = s->dev;
+    const rtc::DevScene& dev = s->dev;
     if (p->accel == RTC_ACCEL_BVH) {
         if (!s->has_bvh) { if (int rc = rtc_scene_build_bvh(s, 0, nullptr)) return rc; }
         bvh = &s->bvh;
-        // the shading kernel fetches the hit triangle through these: one {v0,e1,e2} record per BVH triangle
-        dev.tri_v0 = s->bvh.tris; dev.tri_e1 = s->bvh.tris + 1; dev.tri_e2 = s->bvh.tris + 2; dev.tri_mul = 3u;
     }
     const cudaError_t e = p->math == RTC_MATH_FAST
         ? rtc::fast::launch_render(dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches, bvh)

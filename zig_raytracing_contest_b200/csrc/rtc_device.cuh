@@ -48,7 +48,6 @@ struct DevScene {
     uint32_t shift[3];          // bit position of the block coordinate of x, y, z (6, 6+lx, 6+lx+ly)
     uint32_t coarse_words;
     uint32_t num_materials;
-    uint32_t tri_mul;           // index step of tri_v0/e1/e2: 1 = three SoA arrays (grid), 3 = one {v0,e1,e2} record per triangle (BVH)
 };
 static constexpr uint32_t kMaxGridRes = 1024;     // packed cell: 6 + 3*8 bits
 static constexpr uint32_t kCoarseSmemMaxWords = 8192;   // 32 KiB: the coarse bitmap of a 256^3 grid

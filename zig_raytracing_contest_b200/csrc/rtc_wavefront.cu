@@ -91,17 +91,27 @@ __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const
     __stcs(q.a2 + i, make_float4(e.tx, e.ty, e.tz, __uint_as_float(e.ec)));
     __stcs(q.a3 + i, make_float4(e.dx, e.dy, e.dz, __uint_as_float(e.c)));
 }
-// Appends the rays of the lanes with `push` to the queue: one atomic per warp, order within the warp kept.
+// Appends the rays of the threads with `push` to the queue. Every thread of the CTA calls this (the callers loop a
+// CTA-uniform number of rounds). ONE atomic per CTA and round: the per-warp counts go through shared memory, thread 0
+// reserves the CTA's range. With one atomic per warp the 6.5e5 same-address atomics of a 20 M-ray launch were what
+// k_gen and k_shade waited on (profiles/r2d_*: k_gen at 24 % issue-active while writing 1 GB).
 template <bool BVH>
 __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, bool push, const QueuedRay& e)
 {
-    const uint32_t lane = threadIdx.x & 31u;
+    __shared__ uint32_t s_cnt[kThreads / 32];
+    __shared__ uint32_t s_base;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t m = __ballot_sync(kFull, push);
-    if (m == 0u) return;
-    uint32_t base = 0;
-    if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(count, (uint32_t)__popc(m));
-    base = __shfl_sync(kFull, base, __ffs(m) - 1);
-    if (push) queue_store<BVH>(q, base + __popc(m & ((1u << lane) - 1u)), e);
+    if (lane == 0) s_cnt[warp] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) { const uint32_t c = s_cnt[w]; s_cnt[w] = total; total += c; }
+        s_base = total ? atomicAdd(count, total) : 0u;
+    }
+    __syncthreads();
+    if (push) queue_store<BVH>(q, s_base + s_cnt[warp] + __popc(m & ((1u << lane) - 1u)), e);
 }
 
 // What a new ray needs before it is queued. Grid: Grid.traceRay's iterator (a ray that misses the grid's box is a
@@ -343,6 +353,8 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 //      Triangle.rayIntersection). Tested per lane they ran at 3.5 of 32 lanes (profiles/r2b_*). Winner per ray =
 //      atomicMin on (t bits << 32 | source id) in shared memory: smallest t > 0, smaller source id on exact ties;
 //   C  owners fold their winner in (strictly nearer, or equal and smaller source id) and pop their stack.
+// The hit leaves as {t, u, v, source id} (16 B, in the a3 plane of the input queue, which BVH rays do not use), so
+// the shading kernel neither fetches the triangle again nor repeats its test.
 // The traversal stack is per lane, in local memory (L1-resident: a few entries deep in practice).
 #ifndef RTC_BVH_MINB
 #define RTC_BVH_MINB 4
@@ -357,7 +369,8 @@ struct BvhShared {
     float4 ro[32];                      // per lane: ray origin
     float4 rd[32];                      // per lane: ray direction
     unsigned long long best[32];        // per lane: min over this round's (t bits << 32 | source id)
-    uint32_t win[32];                   // per lane: BVH index of the triangle holding best
+    float2 wuv[32];                     // per lane: u, v of the test holding best (this round)
+    float2 buv[32];                     // per lane: u, v of the ray's nearest hit so far
     uint32_t base[32];                  // per lane: tri_base of its triangle group
     unsigned short pool[kBvhPool];      // (owner lane << 8 | triangle offset) per pooled pair
 };
@@ -365,7 +378,7 @@ struct BvhShared {
 template <bool STATS>
 __global__ void __launch_bounds__(kTraceThreads, RTC_BVH_MINB)
 k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ count_ptr, uint32_t* __restrict__ head_ptr,
-            uint2* __restrict__ hits, unsigned long long* __restrict__ counters)
+            float4* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
     __shared__ BvhShared s_ws[kTraceWarps];
     BvhShared& ws = s_ws[threadIdx.x >> 5];
@@ -433,23 +446,24 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
             for (uint32_t base = 0; base < total; base += 32u) {
                 const uint32_t j = base + lane;
                 unsigned long long key = ~0ull;
-                uint32_t owner = 0u, ti = 0u;
+                uint32_t owner = 0u;
+                float u = 0.0f, v = 0.0f;
                 if (j < total) {
                     const uint32_t e = ws.pool[j];
                     owner = e >> 8;
-                    ti = ws.base[owner] + (e & 0xFFu);
+                    const uint32_t ti = ws.base[owner] + (e & 0xFFu);
                     const float4* p = bv.tris + 3u * (size_t)ti;
                     const float4 a = __ldg(p), e1 = __ldg(p + 1), e2 = __ldg(p + 2);
                     const float4 o4 = ws.ro[owner], d4 = ws.rd[owner];
                     Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
-                    float t, u, v;
+                    float t;
                     if (tri_ray(mk(a.x, a.y, a.z), mk(e1.x, e1.y, e1.z), mk(e2.x, e2.y, e2.z), r, t, u, v) && t > 0.0f) {
                         key = ((unsigned long long)__float_as_uint(t) << 32) | __float_as_uint(a.w);
                         atomicMin(&ws.best[owner], key);
                     }
                 }
                 __syncwarp();
-                if (key != ~0ull && ws.best[owner] == key) ws.win[owner] = ti;     // source ids are unique: one winner
+                if (key != ~0ull && ws.best[owner] == key) ws.wuv[owner] = make_float2(u, v);     // source ids are unique: one winner
                 __syncwarp();
             }
             // ---- C (first half): owners fold the round's winner in ----
@@ -457,17 +471,19 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
                 const unsigned long long k = ws.best[lane];
                 if (k != ~0ull) {
                     const float t = __uint_as_float((uint32_t)(k >> 32));
-                    bool take = s.best_t > t;
-                    if (!take && s.best_t == t && s.best_tri != kMiss)
-                        take = (uint32_t)k < __float_as_uint(__ldg(bv.tris + 3u * (size_t)s.best_tri).w);
-                    if (take) { s.best_t = t; s.best_tri = ws.win[lane]; }
+                    // s.best_tri holds the SOURCE id here (the shading kernel needs nothing else of the triangle)
+                    if (s.best_t > t || (s.best_t == t && (uint32_t)k < s.best_tri)) {
+                        s.best_t = t; s.best_tri = (uint32_t)k; ws.buv[lane] = ws.wuv[lane];
+                    }
                 }
             }
             __syncwarp();
         }
         // ---- C (second half): next group, or the ray is done ----
         if (alive && bvh_step_pop(s, stack, 1u)) {
-            __stcs(hits + qi, make_uint2(__float_as_uint(s.best_t), s.best_tri));
+            // the whole hit travels to the shading kernel: t, u, v and the source triangle (16 B; no triangle fetch there)
+            const float2 uv = s.best_tri != kMiss ? ws.buv[lane] : make_float2(0.0f, 0.0f);
+            __stcs(hits + qi, make_float4(s.best_t, uv.x, uv.y, __uint_as_float(s.best_tri)));
             alive = false;
         }
     }
@@ -522,7 +538,17 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
         QueuedRay e;
         if (i < n) {
             const float4 a0 = __ldcs(qin.a0 + i), a1 = __ldcs(qin.a1 + i);
-            const uint2 h = __ldcs(ws.hits + i);
+            // grid: {t bits, baked triangle}; BVH: {t, u, v, source id} in the a3 plane of the input queue
+            uint2 h;
+            float t = 0.0f, u = 0.0f, v = 0.0f;
+            uint32_t src = kMiss;
+            if (BVH) {
+                const float4 h4 = __ldcs(qin.a3 + i);
+                t = h4.x; u = h4.y; v = h4.z; src = __float_as_uint(h4.w);
+                h = make_uint2(__float_as_uint(h4.x), src);
+            } else {
+                h = __ldcs(ws.hits + i);
+            }
             const uint32_t slot = __float_as_uint(a0.w);
             uint32_t top = __float_as_uint(a1.w);
             Ray ray; ray.o = mk(a0.x, a0.y, a0.z); ray.d = mk(a1.x, a1.y, a1.z);
@@ -541,13 +567,13 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                 }
             } else {
                 cn.hits += 1;
-                // grid: three SoA arrays indexed by the baked triangle; BVH: one record of three float4 per triangle
-                const size_t hi = (size_t)h.y * sc.tri_mul;
-                const float4 ta = __ldg(sc.tri_v0 + hi), tb = __ldg(sc.tri_e1 + hi), tc = __ldg(sc.tri_e2 + hi);
-                float t, u = 0.0f, v = 0.0f;          // the re-test repeats the winning test bit for bit; defined even if it did not
-                tri_ray(mk(ta.x, ta.y, ta.z), mk(tb.x, tb.y, tb.z), mk(tc.x, tc.y, tc.z), ray, t, u, v);
-                t = __uint_as_float(h.x);
-                const uint32_t src = __float_as_uint(ta.w);
+                if (!BVH) {
+                    // the hit's u, v are recomputed from the winning triangle with the arithmetic of the test (same inputs, same bits)
+                    const float4 ta = __ldg(sc.tri_v0 + h.y), tb = __ldg(sc.tri_e1 + h.y), tc = __ldg(sc.tri_e2 + h.y);
+                    tri_ray(mk(ta.x, ta.y, ta.z), mk(tb.x, tb.y, tb.z), mk(tc.x, tc.y, tc.z), ray, t, u, v);
+                    t = __uint_as_float(h.x);
+                    src = __float_as_uint(ta.w);
+                }
                 const TriData td = load_tri_data(sc, src);
                 const DevMaterial* m = sc.materials + td.material;
                 float tu, tv;
@@ -746,7 +772,7 @@ static void run_trace_bvh(const BvhView& bv, const WaveScratch& ws, uint32_t bou
     if (tm && !timed) tm->dropped += 1;
     if (timed) cudaEventRecord(tm->ev[2 * tm->used], cfg.stream);
     kern<<<cfg.sm_count * per_sm, kTraceThreads, 0, cfg.stream>>>(bv, ws.q[bounce & 1u], ws.counts + bounce,
-                                                                   ws.counts + kMaxBounce + 1 + bounce, ws.hits, counters);
+                                                                   ws.counts + kMaxBounce + 1 + bounce, ws.q[bounce & 1u].a3, counters);
     if (timed) { cudaEventRecord(tm->ev[2 * tm->used + 1], cfg.stream); tm->used += 1; }
 }
 

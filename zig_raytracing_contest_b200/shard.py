@@ -79,6 +79,7 @@ def gather_strips(frame, rows, dst=0, group=None):
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     if world == 1:
         return frame
+    frame = frame.contiguous()                    # the strip views below must alias ONE buffer (reshape of a strided frame copies)
     H = frame.shape[0]
     nstrips = (H + rows - 1) // rows
     per_rank = (nstrips + world - 1) // world
