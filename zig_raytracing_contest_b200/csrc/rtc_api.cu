@@ -158,7 +158,7 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
     if (int rc = s->alloc(&d_fine, fine.size())) return rc;
     if (int rc = s->alloc(&d_coarse, coarse.size())) return rc;
     if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
-    if (int rc = s->alloc(&d_data, 5 * (size_t)num_src)) return rc;
+    if (int rc = s->alloc(&d_data, 4 * (size_t)num_src)) return rc;
     static_assert(sizeof(rtc_cell) == sizeof(uint2), "rtc_cell layout");
     CU(cudaMemcpy(d_cells, cells_b.data(), cells_b.size() * sizeof(uint2), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_fine, fine.data(), fine.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
@@ -167,19 +167,18 @@ int scene_upload(rtc_scene* s, const rtc_scene_desc* desc)
         // SoA {v0}{e1}{e2} float4 arrays; v0.w carries the source-triangle id (the reference's rows have
         // an unused 4th lane: @Vector(3,f32) is 16 bytes), so a hit needs no extra index fetch.
         std::vector<float4> pos(3 * M);
-        std::vector<float4> data(5 * (size_t)num_src, make_float4(0, 0, 0, 0));
+        std::vector<float4> data(4 * (size_t)num_src, make_float4(0, 0, 0, 0));
         for (size_t i = 0; i < M; ++i) {
             const rtc_tri_pos& p = desc->tri_pos[i];
             const rtc_tri_data& t = desc->tri_data[i];
             pos[i] = make_float4(p.v0[0], p.v0[1], p.v0[2], __uint_as_float_host(t.src_tri));
             pos[M + i] = make_float4(p.e1[0], p.e1[1], p.e1[2], 0.0f);
             pos[2 * M + i] = make_float4(p.e2[0], p.e2[1], p.e2[2], 0.0f);
-            float w[20] = { 0 };
+            float w[16] = { 0 };
             memcpy(w, t.normal, 9 * sizeof(float));
             memcpy(w + 9, t.texcoord, 6 * sizeof(float));
             memcpy(w + 15, &t.material, sizeof(uint32_t));
-            memcpy(w + 16, &t.src_tri, sizeof(uint32_t));
-            memcpy(&data[5 * (size_t)t.src_tri], w, sizeof w);
+            memcpy(&data[4 * (size_t)t.src_tri], w, sizeof w);
         }
         CU(cudaMemcpy(d_pos, pos.data(), pos.size() * sizeof(float4), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(d_data, data.data(), data.size() * sizeof(float4), cudaMemcpyHostToDevice));

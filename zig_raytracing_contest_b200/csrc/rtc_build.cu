@@ -13,7 +13,7 @@
 //   k_cells     Cell{begin,end} in the reference's x-fastest order + the empty/min/max statistics (stage2.zig:76-100)
 //   k_layout    the same cells by packed index + the two occupancy levels (rtc_device.cuh)
 //   k_bake_soa  bakeInto (stage2.zig:137-164) + Triangle.init (linalg.zig:688-694) into the SoA float4 arrays
-//   k_pack_data Triangle.Data per SOURCE triangle in the 5-float4 layout k_shade reads
+//   k_pack_data Triangle.Data per SOURCE triangle in the 4-float4 (64-byte, sector-aligned) layout k_shade reads
 //   k_bake_aos  the same bake in the C ABI's AoS layout, for rtc_geometry_build_device (parity with the host build)
 //
 // Compiled with -fmad=false, IEEE div/sqrt: the overlap test decides which cells hold a triangle and must
@@ -267,17 +267,15 @@ __global__ void __launch_bounds__(kThreads) k_bake_soa(const unsigned long long*
     e2[i] = make_float4(b.x, b.y, b.z, 0.0f);
 }
 
-// rtc_tri_data (17 words, AoS) -> 5 float4 per source triangle: 9 normal + 6 uv + material + src_tri + 3 pad.
-// flag[0] is set when a material index is out of range.
+// rtc_tri_data (17 words, AoS) -> 4 float4 = 64 B per source triangle: 9 normal + 6 uv + material (the record's index
+// IS the source id). flag[0] is set when a material index is out of range.
 __global__ void __launch_bounds__(kThreads) k_pack_data(const uint32_t* __restrict__ data, uint32_t num_tris, uint32_t num_materials,
                                                         uint32_t* __restrict__ out, uint32_t* __restrict__ flag)
 {
     const uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (i >= (uint64_t)num_tris * 20u) return;
-    const uint32_t t = (uint32_t)(i / 20u), w = (uint32_t)(i % 20u);
-    uint32_t v = 0u;
-    if (w < 16u) v = data[17 * (size_t)t + w];
-    else if (w == 16u) v = t;
+    if (i >= (uint64_t)num_tris * 16u) return;
+    const uint32_t t = (uint32_t)(i / 16u), w = (uint32_t)(i % 16u);
+    const uint32_t v = data[17 * (size_t)t + w];
     if (w == 15u && v >= num_materials) atomicOr(flag, 1u);
     out[i] = v;
 }
@@ -726,7 +724,7 @@ static int scene_from_built(rtc_scene* s, rtc::build::Built& b, uint32_t num_tri
     if (int rc = s->alloc(&d_fine, nb)) return rc;
     if (int rc = s->alloc(&d_coarse, (size_t)d.coarse_words)) return rc;
     if (int rc = s->alloc(&d_pos, 3 * M)) return rc;
-    if (int rc = s->alloc(&d_data, 20 * (size_t)num_tris)) return rc;
+    if (int rc = s->alloc(&d_data, 16 * (size_t)num_tris)) return rc;
     if (int rc = rtc::build::dalloc(&d_flag, 1, &b.tmp)) return rc;
     RTC_CU(cudaMemset(d_cells, 0, nb * 64 * sizeof(uint2)));
     RTC_CU(cudaMemset(d_fine, 0, nb * sizeof(unsigned long long)));
@@ -738,7 +736,7 @@ static int scene_from_built(rtc_scene* s, rtc::build::Built& b, uint32_t num_tri
     rtc::build::k_layout<<<(unsigned)((b.num_cells + kThreads - 1) / kThreads), kThreads>>>(b.d_cells, g, pk, d_cells, d_fine, d_coarse);
     if (M) rtc::build::k_bake_soa<<<(unsigned)((M + kThreads - 1) / kThreads), kThreads>>>(b.d_keys, M, b.d_pos, d_pos, d_pos + M, d_pos + 2 * M);
     if (num_tris) {
-        const uint64_t words = (uint64_t)num_tris * 20u;
+        const uint64_t words = (uint64_t)num_tris * 16u;
         rtc::build::k_pack_data<<<(unsigned)((words + kThreads - 1) / kThreads), kThreads>>>(b.d_data, num_tris, num_materials, d_data, d_flag);
     }
     RTC_CU(cudaGetLastError());

@@ -22,6 +22,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <thread>
@@ -133,10 +134,12 @@ struct Builder {
         while (np < 8) {
             // the pending part most worth splitting: parts too big for a leaf first (largest area), then leaf-sized ones
             int pick = -1; float key = -1.0f; bool pick_big = false;
+            static const int min_split = getenv("RTC_BVH_MINSPLIT") ? atoi(getenv("RTC_BVH_MINSPLIT")) : 2;
+            static const float small_w = getenv("RTC_BVH_SMALLW") ? (float)atof(getenv("RTC_BVH_SMALLW")) : 0.5f;
             for (uint32_t k = 0; k < np; ++k) {
-                if (parts[k].count < 2) continue;
+                if ((int)parts[k].count < min_split) continue;
                 const bool big = parts[k].count > kLeafMax;
-                const float v = parts[k].box.area() * (big ? 1.0f : 0.5f);
+                const float v = parts[k].box.area() * (big ? 1.0f : small_w);
                 if ((big && !pick_big) || (big == pick_big && v > key)) { pick = (int)k; key = v; pick_big = big; }
             }
             if (pick < 0) break;

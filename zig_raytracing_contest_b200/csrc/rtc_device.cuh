@@ -22,7 +22,7 @@ namespace rtc {
 // fine      : uint64[NBP]   bit b = cell b of the block is non-empty. One 8-byte load covers every DDA step a
 //             ray takes inside the block (the per-step occupancy probe was the top stall of the first kernel)
 // coarse    : uint32[NBP/32] bit = block has any triangle; 4 KiB at 128^3 -> staged in shared memory per CTA
-// tri_data  : float4[5*N]   per SOURCE triangle: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat | pad
+// tri_data  : float4[4*N]   per SOURCE triangle, 64 B = two sectors: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x | uv1.y uv2.xy mat
 // texels    : float4[w*h] (rgb, pad) for base colour / emissive, float[w*h] for transparency
 struct DevTexture {
     const void* texels;

@@ -364,6 +364,10 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 #endif
 static constexpr uint32_t kBvhRefillMin = RTC_BVH_REFILL;     // refill when at least this many lanes of the warp are idle
 static constexpr uint32_t kBvhPool = 32u * 24u;               // a lane's triangle group holds at most 24 triangles
+#ifndef RTC_BVH_DIRECT
+#define RTC_BVH_DIRECT 3
+#endif
+static constexpr uint32_t kBvhDirect = RTC_BVH_DIRECT;        // rounds whose busiest lane has at most this many triangles skip the pool
 
 struct BvhShared {
     float4 ro[32];                      // per lane: ray origin
@@ -427,7 +431,27 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
         // ---- B: pooled triangle tests ----
         const uint32_t cnt = __popc(tg.y);
         if (STATS) cn.tris += cnt;
-        if (__ballot_sync(kFull, cnt != 0u) != 0u) {
+        const uint32_t busiest = __reduce_max_sync(kFull, cnt);
+        if (busiest != 0u && busiest <= kBvhDirect) {
+            // few triangles per lane (the incoherent case): pooling would cost more (scan, pool fill, atomics, two
+            // warp barriers per pass) than the passes it saves — every lane tests its own, `busiest` passes
+            if (cnt != 0u) {
+                const float4 o4 = ws.ro[lane], d4 = ws.rd[lane];
+                Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
+                uint32_t m = tg.y;
+                do {
+                    const uint32_t b = 31u - (uint32_t)__clz((int)m);
+                    m &= ~(1u << b);
+                    const float4* p = bv.tris + 3u * (size_t)(tg.x + b);
+                    const float4 a = __ldg(p), e1 = __ldg(p + 1), e2 = __ldg(p + 2);
+                    float t, u, v;
+                    if (tri_ray(mk(a.x, a.y, a.z), mk(e1.x, e1.y, e1.z), mk(e2.x, e2.y, e2.z), r, t, u, v) && t > 0.0f) {
+                        const uint32_t src = __float_as_uint(a.w);
+                        if (s.best_t > t || (s.best_t == t && src < s.best_tri)) { s.best_t = t; s.best_tri = src; ws.buv[lane] = make_float2(u, v); }
+                    }
+                } while (m != 0u);
+            }
+        } else if (busiest != 0u) {
             uint32_t incl = cnt;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, d); if (lane >= (uint32_t)d) incl += v; }
@@ -491,11 +515,11 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Triangle.Data (src/stage3.zig:42-71) as stored on the device: 5 float4 per SOURCE triangle.
+// Triangle.Data (src/stage3.zig:42-71) as stored on the device: 4 float4 (64 B) per SOURCE triangle.
 struct TriData { v3 n0, n1, n2; float uv0[2], uv1[2], uv2[2]; uint32_t material; };
 __device__ __forceinline__ TriData load_tri_data(const DevScene& sc, uint32_t src)
 {
-    const float4* p = sc.tri_data + 5u * (size_t)src;
+    const float4* p = sc.tri_data + 4u * (size_t)src;
     const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2), q3 = __ldg(p + 3);
     TriData d;
     d.n0 = mk(q0.x, q0.y, q0.z); d.n1 = mk(q0.w, q1.x, q1.y); d.n2 = mk(q1.z, q1.w, q2.x);
@@ -521,8 +545,13 @@ __device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, fl
 // RNG block 1 + bounce of the path: draw 0 = the alpha test (always drawn, stage3.zig:207), draws 1, 2 = the
 // scatter direction. A scattering level pushes (emissive, albedo) for k_accum; an alpha pass-through level
 // (stage3.zig:207-213) consumes a depth level and neither attenuates nor pushes.
+#ifndef RTC_SHADE_MINB
+#define RTC_SHADE_MINB 4
+#endif
+static constexpr uint32_t kMatSmem = 32;             // material tables up to this size are staged in shared memory
+
 template <bool PRIMARY, bool BVH>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, RTC_SHADE_MINB)
 k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera cam, const __grid_constant__ WaveParams wp,
         const __grid_constant__ WaveScratch ws, uint32_t bounce, PrimaryOut out, unsigned long long* __restrict__ counters)
 {
@@ -532,6 +561,16 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
     const uint32_t stride = gridDim.x * kThreads;
     const uint32_t rounds = (n + stride - 1u) / stride;
     const float eps = 1.1920928955078125e-07f;           // std.math.floatEps(f32)
+    // the material table (three texture headers per material) sits in shared memory: one level less in the chain of
+    // dependent global loads hit -> triangle data -> material -> texels
+    __shared__ DevMaterial s_mats[kMatSmem];
+    const bool msm = sc.num_materials <= kMatSmem;
+    if (msm) {
+        const uint32_t words = sc.num_materials * (uint32_t)(sizeof(DevMaterial) / 4u);
+        for (uint32_t k = threadIdx.x; k < words; k += kThreads)
+            reinterpret_cast<uint32_t*>(s_mats)[k] = __ldg(reinterpret_cast<const uint32_t*>(sc.materials) + k);
+        __syncthreads();
+    }
     for (uint32_t it = 0; it < rounds; ++it) {
         const uint32_t i = it * stride + blockIdx.x * kThreads + threadIdx.x;
         bool push = false;
@@ -575,7 +614,7 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
                     src = __float_as_uint(ta.w);
                 }
                 const TriData td = load_tri_data(sc, src);
-                const DevMaterial* m = sc.materials + td.material;
+                const DevMaterial* m = (msm ? s_mats : sc.materials) + td.material;
                 float tu, tv;
                 interp_uv(td, u, v, tu, tv);
                 if (PRIMARY) {
