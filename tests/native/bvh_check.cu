@@ -23,14 +23,14 @@ int bvh_check(const float* tris, uint32_t n, const float* rays, uint32_t m, int 
     const int rc = rtc_bvh_build_host(tris, n, threads, h);
     if (rc != 0) return -1000 + rc;
     // BVH-ordered triangle records with the input index as the source id
-    std::vector<float4> bt(3 * (size_t)n + 3);
+    std::vector<float4> bt(kBvhTriQuads * (size_t)n + kBvhTriQuads);
     for (uint32_t k = 0; k < n; ++k) {
         const uint32_t i = h.order[k];
         const float* t = tris + 12 * (size_t)i;
         float w; memcpy(&w, &i, 4);
-        bt[3 * (size_t)k] = make_float4(t[0], t[1], t[2], w);
-        bt[3 * (size_t)k + 1] = make_float4(t[4], t[5], t[6], 0.0f);
-        bt[3 * (size_t)k + 2] = make_float4(t[8], t[9], t[10], 0.0f);
+        bt[kBvhTriQuads * (size_t)k] = make_float4(t[0], t[1], t[2], w);
+        bt[kBvhTriQuads * (size_t)k + 1] = make_float4(t[4], t[5], t[6], 0.0f);
+        bt[kBvhTriQuads * (size_t)k + 2] = make_float4(t[8], t[9], t[10], 0.0f);
     }
     // every input triangle exactly once
     {

@@ -73,6 +73,10 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t[0])
 
+    # one-off allocations (the pinned host frame, the wavefront scratch, NCCL's channels) happen here, not in a timed row
+    scene.render_sharded(comm, cam, rtc.make_params(num_samples=1, max_bounce=4, seed=1, accel=abi.RTC_ACCEL_BVH,
+                                                    shard=abi.RTC_SHARD_STRIPS if args.strips else abi.RTC_SHARD_SAMPLES),
+                         img=img if rank == 0 else None, to_host=True)
     rows = []
     shard = abi.RTC_SHARD_STRIPS if args.strips else abi.RTC_SHARD_SAMPLES
     plan = [("bvh", s) for s in args.spp] + [("grid", s) for s in args.grid_spp]

@@ -678,21 +678,23 @@ int rtc_scene_build_bvh(rtc_scene* s, int num_threads, rtc_bvh_info* info)
     const int brc = rtc_bvh_build_host(rec.data(), N, num_threads, h);
     if (brc != 0) return fail(RTC_ERR_UNSUPPORTED, "BVH build failed (code %d): coordinates outside the quantisation range or a leaf overflow", brc);
     if (h.depth + 1 >= rtc::kBvhStack) return fail(RTC_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack (%u)", h.depth, rtc::kBvhStack);
-    std::vector<float4> bt(3 * (size_t)N + 3, make_float4(0, 0, 0, 0));
+    const size_t TQ = rtc::kBvhTriQuads, NQ = rtc::kBvhNodeQuads;
+    std::vector<float4> bt(TQ * (size_t)N + TQ, make_float4(0, 0, 0, 0));
     for (uint32_t k = 0; k < N; ++k) {
         const float* r = &rec[12 * (size_t)h.order[k]];
-        bt[3 * (size_t)k] = make_float4(r[0], r[1], r[2], r[3]);
-        bt[3 * (size_t)k + 1] = make_float4(r[4], r[5], r[6], 0.0f);
-        bt[3 * (size_t)k + 2] = make_float4(r[8], r[9], r[10], 0.0f);
+        bt[TQ * (size_t)k] = make_float4(r[0], r[1], r[2], r[3]);
+        bt[TQ * (size_t)k + 1] = make_float4(r[4], r[5], r[6], 0.0f);
+        bt[TQ * (size_t)k + 2] = make_float4(r[8], r[9], r[10], 0.0f);
     }
     float4* d_nodes = nullptr; float4* d_tris = nullptr;
-    if (int rc = s->alloc(&d_nodes, 5 * (size_t)h.num_nodes)) return rc;
+    if (h.nodes.size() != 4 * NQ * (size_t)h.num_nodes) return fail(RTC_ERR_CUDA, "BVH builder returned %zu words for %u nodes", h.nodes.size(), h.num_nodes);
+    if (int rc = s->alloc(&d_nodes, NQ * (size_t)h.num_nodes)) return rc;
     if (int rc = s->alloc(&d_tris, bt.size())) return rc;
-    CU(cudaMemcpy(d_nodes, h.nodes.data(), 80 * (size_t)h.num_nodes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_nodes, h.nodes.data(), 16 * NQ * (size_t)h.num_nodes, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_tris, bt.data(), bt.size() * sizeof(float4), cudaMemcpyHostToDevice));
     s->bvh.nodes = d_nodes; s->bvh.tris = d_tris;
     s->bvh_info.num_nodes = h.num_nodes; s->bvh_info.num_tris = N; s->bvh_info.depth = h.depth; s->bvh_info.reserved = 0;
-    s->bvh_info.bytes = 80ull * h.num_nodes + 48ull * N;
+    s->bvh_info.bytes = 16ull * NQ * h.num_nodes + 16ull * TQ * N;
     s->bvh_info.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     s->has_bvh = true;
     if (info) *info = s->bvh_info;

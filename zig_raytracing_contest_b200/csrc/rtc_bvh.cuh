@@ -13,7 +13,9 @@
 // The functions are __host__ __device__: tests/native/bvh_check.cu runs the same node test and step function on the
 // CPU against a brute-force loop over all triangles.
 //
-// NODE (80 B = 5 x 16 B, after Ylitie, Karras, Laine, "Efficient Incoherent Ray Traversal on GPUs Through Compressed
+// NODE (80 B of content = 5 x 16 B, stored at a 96-byte stride so that a node is exactly three 32-byte sectors and is
+// fetched with three 256-bit loads (LDG.256, sm_100) instead of five 128-bit loads that touch 3-4 sectors; after
+// Ylitie, Karras, Laine, "Efficient Incoherent Ray Traversal on GPUs Through Compressed
 // Wide BVHs", HPG 2017 — the published layout, written from the paper):
 //   q0: p.x p.y p.z | ex, ey, ez, imask        origin of the quantisation frame, biased exponents of the per-axis
 //                                              scale 2^e, bit s of imask = slot s holds an inner node
@@ -33,9 +35,26 @@
 namespace rtc {
 
 struct BvhView {
-    const float4* nodes;       // 5 float4 per node; node 0 = root
-    const float4* tris;        // 3 float4 per triangle in BVH order: {v0 | src id} {e1} {e2}
+    const float4* nodes;       // kBvhNodeQuads float4 per node (5 used + 1 pad: 96 B, sector-aligned); node 0 = root
+    const float4* tris;        // kBvhTriQuads float4 per triangle in BVH order: {v0 | src id} {e1} {e2} {pad}: 64 B, two sectors
 };
+static constexpr uint32_t kBvhNodeQuads = 6;
+static constexpr uint32_t kBvhTriQuads = 4;
+
+// 32 bytes in one request: one sector, one L1 tag lookup (the records above are laid out for it)
+struct Quad2 { float4 lo, hi; };
+RTC_HD Quad2 bvh_ld256(const float4* p)
+{
+    Quad2 r;
+#ifdef __CUDA_ARCH__
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
+        : "l"(p));
+#else
+    r.lo = p[0]; r.hi = p[1];
+#endif
+    return r;
+}
 
 struct BvhRay {
     float ox, oy, oz;
@@ -96,8 +115,9 @@ RTC_HD void bvh_ray_init(BvhRay& r, v3 o, v3 d)
 // leaf children that were hit}.
 RTC_HD void bvh_node_hits(const float4* __restrict__ nodes, uint32_t ni, const BvhRay& r, float tmax, uint2& ng, uint2& tg)
 {
-    const float4* n = nodes + 5u * (size_t)ni;
-    const float4 q0 = RTC_LDG(n), q1 = RTC_LDG(n + 1), q2 = RTC_LDG(n + 2), q3 = RTC_LDG(n + 3), q4 = RTC_LDG(n + 4);
+    const float4* n = nodes + kBvhNodeQuads * (size_t)ni;
+    const Quad2 n01 = bvh_ld256(n), n23 = bvh_ld256(n + 2), n45 = bvh_ld256(n + 4);
+    const float4 q0 = n01.lo, q1 = n01.hi, q2 = n23.lo, q3 = n23.hi, q4 = n45.lo;
     const uint32_t eim = f_bits(q0.w);
     const float sx = bvh_u2f((eim & 0xFFu) << 23) * r.ix;
     const float sy = bvh_u2f(((eim >> 8) & 0xFFu) << 23) * r.iy;
@@ -154,13 +174,13 @@ RTC_HD void bvh_trav_begin(BvhTrav& s)
 // The reference's acceptance `nearest.t > hit.t and hit.t > 0` (stage3.zig:174); on an exact tie the smaller source id.
 RTC_HD void bvh_test_tri(const BvhView& b, const Ray& ray, uint32_t ti, BvhTrav& s)
 {
-    const float4* p = b.tris + 3u * (size_t)ti;
+    const float4* p = b.tris + kBvhTriQuads * (size_t)ti;
     const float4 a = RTC_LDG(p), e1 = RTC_LDG(p + 1), e2 = RTC_LDG(p + 2);
     float t, u, v;
     if (!tri_ray(mk(a.x, a.y, a.z), mk(e1.x, e1.y, e1.z), mk(e2.x, e2.y, e2.z), ray, t, u, v) || !(t > 0.0f)) return;
     if (s.best_t > t) { s.best_t = t; s.best_tri = ti; return; }
     if (s.best_t == t && s.best_tri != 0xFFFFFFFFu) {
-        const uint32_t cur = f_bits(RTC_LDG(b.tris + 3u * (size_t)s.best_tri).w);
+        const uint32_t cur = f_bits(RTC_LDG(b.tris + kBvhTriQuads * (size_t)s.best_tri).w);
         if (f_bits(a.w) < cur) s.best_tri = ti;
     }
 }

@@ -181,7 +181,7 @@ int rtc_bvh_build_host(const float* tris, uint32_t n, int threads, RtcBvhHost& o
     out.nodes.clear(); out.order.clear(); out.depth = 0; out.num_nodes = 0;
     if (n == 0) {
         // one empty root: every slot empty, nothing is ever hit
-        out.nodes.assign(20, 0u);
+        out.nodes.assign(24, 0u);
         const float one = 1.0f; uint32_t e; memcpy(&e, &one, 4);
         out.nodes[3] = (e >> 23) * 0x00010101u;
         out.num_nodes = 1;
@@ -255,7 +255,7 @@ int rtc_bvh_build_host(const float* tris, uint32_t n, int threads, RtcBvhHost& o
     std::vector<Item> queue;
     queue.push_back({ 0u, 0u });
     uint32_t next_node = 1;
-    out.nodes.assign(20, 0u);
+    out.nodes.assign(24, 0u);
     out.order.reserve(n);
     for (size_t qi = 0; qi < queue.size(); ++qi) {
         const Item it = queue[qi];
@@ -334,8 +334,8 @@ int rtc_bvh_build_host(const float* tris, uint32_t n, int threads, RtcBvhHost& o
         memcpy(&w[6], meta, 8);
         memcpy(&w[8], q[0], 8); memcpy(&w[10], q[1], 8); memcpy(&w[12], q[2], 8);
         memcpy(&w[14], q[3], 8); memcpy(&w[16], q[4], 8); memcpy(&w[18], q[5], 8);
-        if (out.nodes.size() < 20 * (size_t)next_node) out.nodes.resize(20 * (size_t)next_node, 0u);
-        memcpy(&out.nodes[20 * (size_t)it.onode], w, sizeof w);
+        if (out.nodes.size() < 24 * (size_t)next_node) out.nodes.resize(24 * (size_t)next_node, 0u);
+        memcpy(&out.nodes[24 * (size_t)it.onode], w, sizeof w);       // 80 bytes of content at a 96-byte stride
     }
     out.num_nodes = next_node;
     if (out.order.size() != n) return -3;

@@ -5,7 +5,7 @@
 #include <vector>
 
 struct RtcBvhHost {
-    std::vector<uint32_t> nodes;     // 20 words (80 bytes) per node, layout in rtc_bvh.cuh; node 0 = root
+    std::vector<uint32_t> nodes;     // 24 words per node (80 bytes of content at a 96-byte stride), layout in rtc_bvh.cuh; node 0 = root
     std::vector<uint32_t> order;     // BVH triangle slot -> index of the input triangle
     uint32_t num_nodes = 0;
     uint32_t depth = 0;              // levels of inner nodes (bounds the traversal stack)

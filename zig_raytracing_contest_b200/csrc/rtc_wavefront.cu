@@ -442,8 +442,9 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
                 do {
                     const uint32_t b = 31u - (uint32_t)__clz((int)m);
                     m &= ~(1u << b);
-                    const float4* p = bv.tris + 3u * (size_t)(tg.x + b);
-                    const float4 a = __ldg(p), e1 = __ldg(p + 1), e2 = __ldg(p + 2);
+                    const float4* p = bv.tris + kBvhTriQuads * (size_t)(tg.x + b);
+                    const Quad2 t01 = bvh_ld256(p), t23 = bvh_ld256(p + 2);
+                    const float4 a = t01.lo, e1 = t01.hi, e2 = t23.lo;
                     float t, u, v;
                     if (tri_ray(mk(a.x, a.y, a.z), mk(e1.x, e1.y, e1.z), mk(e2.x, e2.y, e2.z), r, t, u, v) && t > 0.0f) {
                         const uint32_t src = __float_as_uint(a.w);
@@ -476,8 +477,9 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
                     const uint32_t e = ws.pool[j];
                     owner = e >> 8;
                     const uint32_t ti = ws.base[owner] + (e & 0xFFu);
-                    const float4* p = bv.tris + 3u * (size_t)ti;
-                    const float4 a = __ldg(p), e1 = __ldg(p + 1), e2 = __ldg(p + 2);
+                    const float4* p = bv.tris + kBvhTriQuads * (size_t)ti;
+                    const Quad2 t01 = bvh_ld256(p), t23 = bvh_ld256(p + 2);
+                    const float4 a = t01.lo, e1 = t01.hi, e2 = t23.lo;
                     const float4 o4 = ws.ro[owner], d4 = ws.rd[owner];
                     Ray r; r.o = mk(o4.x, o4.y, o4.z); r.d = mk(d4.x, d4.y, d4.z);
                     float t;
