@@ -46,12 +46,12 @@ struct Quad2 { float4 lo, hi; };
 RTC_HD Quad2 bvh_ld256(const float4* p)
 {
     Quad2 r;
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && !defined(RTC_BVH_NO_LD256)
     asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
         : "l"(p));
 #else
-    r.lo = p[0]; r.hi = p[1];
+    r.lo = RTC_LDG(p); r.hi = RTC_LDG(p + 1);
 #endif
     return r;
 }

@@ -95,23 +95,57 @@ __device__ __forceinline__ void queue_store(const RayQueue& q, uint32_t i, const
 // CTA-uniform number of rounds). ONE atomic per CTA and round: the per-warp counts go through shared memory, thread 0
 // reserves the CTA's range. With one atomic per warp the 6.5e5 same-address atomics of a 20 M-ray launch were what
 // k_gen and k_shade waited on (profiles/r2d_*: k_gen at 24 % issue-active while writing 1 GB).
+#ifndef RTC_QSORT
+#define RTC_QSORT 0
+#endif
 template <bool BVH>
 __device__ __forceinline__ void queue_push(const RayQueue& q, uint32_t* count, bool push, const QueuedRay& e)
 {
-    __shared__ uint32_t s_cnt[kThreads / 32];
-    __shared__ uint32_t s_base;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    constexpr int kWarps = kThreads / 32;
+#if RTC_QSORT
+    // EXPERIMENT, off by default (profiles/r2j_ab_*: the traversal kernels gain 0.2 % from it, k_gen / k_shade pay 3.5 ms
+    // per frame for the sort: 2974 vs 3041 Mrays/s with the BVH, 1778 vs 1809 with the grid).
+    // The CTA's rays of this round go out GROUPED BY DIRECTION OCTANT (a counting sort over 8 buckets in shared
+    // memory): consecutive queue entries — the rays one traversal warp picks up together — then share the sign of every
+    // direction component, i.e. the DDA's step directions / the BVH's child order, and they come from neighbouring
+    // pixels. The order of the queue has no influence on the results (every ray carries its slot).
+    __shared__ uint32_t s_cnt[8 * kWarps];              // [bucket][warp] -> count, then exclusive offset inside the CTA's range
+    __shared__ uint32_t s_base;
+    if (threadIdx.x < 8 * kWarps) s_cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t bkt = push ? ((e.r.d.x < 0.0f ? 1u : 0u) | (e.r.d.y < 0.0f ? 2u : 0u) | (e.r.d.z < 0.0f ? 4u : 0u)) : 8u;
+    const uint32_t peers = __match_any_sync(kFull, bkt);
+    const uint32_t rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
+    if (push && rank == 0u) s_cnt[bkt * kWarps + warp] = (uint32_t)__popc(peers);
+    __syncthreads();
+    if (warp == 0) {
+        // exclusive scan of the 64 counts in bucket-major order: two per lane
+        const uint32_t c0 = s_cnt[2u * lane], c1 = s_cnt[2u * lane + 1u];
+        uint32_t incl = c0 + c1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, d); if (lane >= (uint32_t)d) incl += v; }
+        const uint32_t excl = incl - (c0 + c1);
+        s_cnt[2u * lane] = excl; s_cnt[2u * lane + 1u] = excl + c0;
+        if (lane == 31u) s_base = incl ? atomicAdd(count, incl) : 0u;
+    }
+    __syncthreads();
+    if (push) queue_store<BVH>(q, s_base + s_cnt[bkt * kWarps + warp] + rank, e);
+#else
+    __shared__ uint32_t s_cnt[kWarps];
+    __shared__ uint32_t s_base;
     const uint32_t m = __ballot_sync(kFull, push);
     if (lane == 0) s_cnt[warp] = (uint32_t)__popc(m);
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t total = 0;
 #pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) { const uint32_t c = s_cnt[w]; s_cnt[w] = total; total += c; }
+        for (int w = 0; w < kWarps; ++w) { const uint32_t c = s_cnt[w]; s_cnt[w] = total; total += c; }
         s_base = total ? atomicAdd(count, total) : 0u;
     }
     __syncthreads();
     if (push) queue_store<BVH>(q, s_base + s_cnt[warp] + __popc(m & ((1u << lane) - 1u)), e);
+#endif
 }
 
 // What a new ray needs before it is queued. Grid: Grid.traceRay's iterator (a ray that misses the grid's box is a
