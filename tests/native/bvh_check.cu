@@ -37,7 +37,7 @@ int bvh_check(const float* tris, uint32_t n, const float* rays, uint32_t m, int 
         std::vector<uint8_t> seen(n, 0);
         for (uint32_t k = 0; k < n; ++k) { if (h.order[k] >= n || seen[h.order[k]]) return -2000; seen[h.order[k]] = 1; }
     }
-    BvhView view; view.nodes = reinterpret_cast<const float4*>(h.nodes.data()); view.tris = bt.data();
+    BvhView view; view.num_nodes = h.num_nodes; view.nodes = reinterpret_cast<const float4*>(h.nodes.data()); view.tris = bt.data();
     uint64_t visits = 0, tests = 0, max_sp = 0;
     int bad = 0;
     for (uint32_t r = 0; r < m; ++r) {

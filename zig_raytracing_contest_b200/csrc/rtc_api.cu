@@ -692,7 +692,7 @@ int rtc_scene_build_bvh(rtc_scene* s, int num_threads, rtc_bvh_info* info)
     if (int rc = s->alloc(&d_tris, bt.size())) return rc;
     CU(cudaMemcpy(d_nodes, h.nodes.data(), 16 * NQ * (size_t)h.num_nodes, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d_tris, bt.data(), bt.size() * sizeof(float4), cudaMemcpyHostToDevice));
-    s->bvh.nodes = d_nodes; s->bvh.tris = d_tris;
+    s->bvh.nodes = d_nodes; s->bvh.tris = d_tris; s->bvh.num_nodes = h.num_nodes;
     s->bvh_info.num_nodes = h.num_nodes; s->bvh_info.num_tris = N; s->bvh_info.depth = h.depth; s->bvh_info.reserved = 0;
     s->bvh_info.bytes = 16ull * NQ * h.num_nodes + 16ull * TQ * N;
     s->bvh_info.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

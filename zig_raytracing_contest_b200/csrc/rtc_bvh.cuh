@@ -35,6 +35,7 @@
 namespace rtc {
 
 struct BvhView {
+    uint32_t num_nodes;
     const float4* nodes;       // kBvhNodeQuads float4 per node (5 used + 1 pad: 96 B, sector-aligned); node 0 = root
     const float4* tris;        // kBvhTriQuads float4 per triangle in BVH order: {v0 | src id} {e1} {e2} {pad}: 64 B, two sectors
 };
@@ -113,11 +114,20 @@ RTC_HD void bvh_ray_init(BvhRay& r, v3 o, v3 d)
 // Slab test of the ray against the (up to) eight quantised child boxes of node ni, clipped to [0, tmax]. Fills the
 // node group {child_base, inner hits << 24 | imask} and the triangle group {tri_base, one bit per triangle of the
 // leaf children that were hit}.
-RTC_HD void bvh_node_hits(const float4* __restrict__ nodes, uint32_t ni, const BvhRay& r, float tmax, uint2& ng, uint2& tg)
+// `top` (may be null): the first `ntop` nodes — breadth-first order, i.e. the top levels of the tree, which every ray
+// visits — as 5 float4 each in shared memory (k_trace_bvh stages them once per CTA): no L1 tag lookups for them.
+RTC_HD void bvh_node_hits(const float4* __restrict__ nodes, const float4* top, uint32_t ntop, uint32_t ni, const BvhRay& r, float tmax,
+                          uint2& ng, uint2& tg)
 {
-    const float4* n = nodes + kBvhNodeQuads * (size_t)ni;
-    const Quad2 n01 = bvh_ld256(n), n23 = bvh_ld256(n + 2), n45 = bvh_ld256(n + 4);
-    const float4 q0 = n01.lo, q1 = n01.hi, q2 = n23.lo, q3 = n23.hi, q4 = n45.lo;
+    float4 q0, q1, q2, q3, q4;
+    if (ni < ntop) {
+        const float4* n = top + 5u * ni;
+        q0 = n[0]; q1 = n[1]; q2 = n[2]; q3 = n[3]; q4 = n[4];
+    } else {
+        const float4* n = nodes + kBvhNodeQuads * (size_t)ni;
+        const Quad2 n01 = bvh_ld256(n), n23 = bvh_ld256(n + 2), n45 = bvh_ld256(n + 4);
+        q0 = n01.lo; q1 = n01.hi; q2 = n23.lo; q3 = n23.hi; q4 = n45.lo;
+    }
     const uint32_t eim = f_bits(q0.w);
     const float sx = bvh_u2f((eim & 0xFFu) << 23) * r.ix;
     const float sy = bvh_u2f(((eim >> 8) & 0xFFu) << 23) * r.iy;
@@ -191,7 +201,8 @@ RTC_HD void bvh_test_tri(const BvhView& b, const Ray& ray, uint32_t ti, BvhTrav&
 // off the stack when the current one is used up; returns true when the ray is done.
 // nodes counts what the STATS build reports (80-byte node records fetched).
 template <bool STATS>
-RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2* stack, uint32_t stride, uint32_t& nodes)
+RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2* stack, uint32_t stride, uint32_t& nodes,
+                            const float4* top = nullptr, uint32_t ntop = 0u)
 {
     uint2 tg;
     if (s.ng.y > 0x00FFFFFFu) {
@@ -202,7 +213,7 @@ RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2
         const uint32_t slot = (bit - 24u) ^ (r.octinv4 & 7u);
         const uint32_t rel = bvh_popc(hits & ~(0xFFFFFFFFu << slot));
         if (STATS) nodes += 1u;
-        bvh_node_hits(b.nodes, s.ng.x + rel, r, s.best_t, s.ng, tg);
+        bvh_node_hits(b.nodes, top, ntop, s.ng.x + rel, r, s.best_t, s.ng, tg);
     } else {
         tg = s.ng;
         s.ng = make_uint2(0u, 0u);

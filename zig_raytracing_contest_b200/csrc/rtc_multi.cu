@@ -93,7 +93,7 @@ int rtc_scene_clone_(const rtc_scene* src, int device, rtc_scene** out)
     }
     r->has_bvh = src->has_bvh;
     r->bvh_info = src->bvh_info;
-    if (src->has_bvh) { r->bvh.nodes = (const float4*)tr(src->bvh.nodes); r->bvh.tris = (const float4*)tr(src->bvh.tris); }
+    if (src->has_bvh) { r->bvh.nodes = (const float4*)tr(src->bvh.nodes); r->bvh.tris = (const float4*)tr(src->bvh.tris); r->bvh.num_nodes = src->bvh.num_nodes; }
     if (lost) return bail(rtc_fail_(RTC_ERR_CUDA, "replica: a scene pointer lies outside the scene's allocations"));
     r->num_tris = src->num_tris; r->num_src_tris = src->num_src_tris;
     r->is_replica = true;
@@ -130,7 +130,7 @@ int ensure_replicas(rtc_scene* s, const std::vector<int>& devices)
             rtc_scene_free_(r);
             s->replicas[g - 1] = nullptr;
             rtc_scene* fresh = nullptr;
-            if (int rc = rtc_scene_clone_(s, devices[g], &fresh)) { s->replicas.resize(g - 1); return rc; }
+            if (int rc = rtc_scene_clone_(s, devices[g], &fresh)) { s->replicas.erase(s->replicas.begin() + (long)(g - 1)); return rc; }
             s->replicas[g - 1] = fresh;
             continue;
         }

@@ -398,6 +398,13 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 #endif
 static constexpr uint32_t kBvhRefillMin = RTC_BVH_REFILL;     // refill when at least this many lanes of the warp are idle
 static constexpr uint32_t kBvhPool = 32u * 24u;               // a lane's triangle group holds at most 24 triangles
+#ifndef RTC_BVH_TOP
+#define RTC_BVH_TOP 0
+#endif
+// Nodes staged in shared memory (breadth-first order = the top levels). EXPERIMENT, off: 9 nodes +0.4 %, 73 or 256 nodes
+// -0.9 % on the atrium, -1.9 % on the 5 M-triangle scene (profiles/r2l_ab_*): the per-node branch between the two
+// fetch paths costs what the saved L1 lookups give.
+static constexpr uint32_t kBvhTop = RTC_BVH_TOP;
 #ifndef RTC_BVH_DIRECT
 #define RTC_BVH_DIRECT 3
 #endif
@@ -419,10 +426,15 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
             float4* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
     __shared__ BvhShared s_ws[kTraceWarps];
+    __shared__ float4 s_top[kBvhTop > 0u ? 5u * kBvhTop : 1u];
     BvhShared& ws = s_ws[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t n = __ldg(count_ptr);
+    // the top of the tree (breadth-first node order: the first nodes are the first levels), once per CTA
+    const uint32_t ntop = bv.num_nodes < kBvhTop ? bv.num_nodes : kBvhTop;
+    for (uint32_t k = threadIdx.x; k < 5u * ntop; k += kTraceThreads) s_top[k] = __ldg(bv.nodes + kBvhNodeQuads * (k / 5u) + (k % 5u));
+    __syncthreads();
     Counters cn = { 0, 0, 0, 0, 0 };
     uint32_t next = 0, end = 0;
     bool exhausted = false, alive = false;
@@ -461,7 +473,7 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
         }
         // ---- A: one node per live lane ----
         uint2 tg = make_uint2(0u, 0u);
-        if (alive) tg = bvh_step_nodes<STATS>(bv, br, s, stack, 1u, cn.cells);
+        if (alive) tg = bvh_step_nodes<STATS>(bv, br, s, stack, 1u, cn.cells, s_top, ntop);
         // ---- B: pooled triangle tests ----
         const uint32_t cnt = __popc(tg.y);
         if (STATS) cn.tris += cnt;
