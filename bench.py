@@ -322,8 +322,7 @@ def run_gpu(args, rank, world, local_rank):
     one = scene.render(cam, prm, img=img, want_stats=True, instrumented=False)["stats"] if inproc > 1 else \
         scene.render_sharded(comm, cam, prm, to_host=False, want_stats=True)["stats"]
     if inproc > 1:
-        r[0], r[1], r[2] = one["rays"] * args.steps, one["paths"] * args.steps, one["launches"] * args.steps
-        trace_ms, trace_launches = one["trace_ms"] / inproc, one["trace_launches"] / inproc
+        trace_ms, trace_launches = trace_ms / inproc, trace_launches / inproc      # summed over the devices: per device
     rays_per_step = float(r[0]) / args.steps
     launches = int(round(float(r[2]) / args.steps))
     value = rays_per_step / (step_ms * 1e-3) / 1e6

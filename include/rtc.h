@@ -263,8 +263,8 @@ int rtc_render_accumulate(rtc_scene* scene, const rtc_camera* camera, const rtc_
 int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples,
                 void* d_rgb, void* d_radiance, int device, void* stream);
 
-/* Fetches and clears the ray/traversal counters accumulated on the scene's device
- * since the last call (synchronises the device). */
+/* Fetches and clears the ray/traversal counters accumulated on the scene's device — and, after num_gpus > 1 renders,
+ * on its replicas' devices (summed) — since the last call (synchronises those devices). */
 int rtc_scene_stats(rtc_scene* scene, rtc_stats* out);
 
 /* RTC_ACCEL_BVH's structure: built on the host threads (num_threads < 1 = all) from the scene's own device-resident

@@ -704,10 +704,24 @@ int rtc_scene_build_bvh(rtc_scene* s, int num_threads, rtc_bvh_info* info)
 int rtc_scene_stats(rtc_scene* s, rtc_stats* out)
 {
     if (!s || !out) return fail(RTC_ERR_INVALID_ARGUMENT, "null argument");
-    DeviceGuard guard(s->device);
-    CU(cudaDeviceSynchronize());
     memset(out, 0, sizeof *out);
-    return read_counters(s, out);
+    {
+        DeviceGuard guard(s->device);
+        CU(cudaDeviceSynchronize());
+        if (int rc = read_counters(s, out)) return rc;
+    }
+    // a scene that has rendered with num_gpus > 1: its replicas' counters belong to it (summed, cleared)
+    for (rtc_scene* r : s->replicas) {
+        DeviceGuard guard(r->device);
+        CU(cudaDeviceSynchronize());
+        rtc_stats st;
+        memset(&st, 0, sizeof st);
+        if (int rc = read_counters(r, &st)) return rc;
+        out->rays += st.rays; out->cells_visited += st.cells_visited; out->tris_tested += st.tris_tested;
+        out->hits_shaded += st.hits_shaded; out->paths += st.paths; out->launches += st.launches;
+        out->trace_ms += st.trace_ms; out->trace_launches += st.trace_launches; out->trace_launches_untimed += st.trace_launches_untimed;
+    }
+    return RTC_OK;
 }
 
 }  // extern "C"

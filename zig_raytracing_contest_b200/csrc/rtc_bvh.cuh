@@ -1,5 +1,5 @@
-// rtc_bvh.cuh — the opt-in RTC_ACCEL_BVH traversal: an 8-wide BVH with quantised child boxes (80-byte nodes, five
-// 128-bit loads) over the scene's source triangles, walked per lane with a short stack. It replaces the reference's
+// rtc_bvh.cuh — the opt-in RTC_ACCEL_BVH traversal: an 8-wide BVH with quantised child boxes (80-byte nodes fetched as
+// three 256-bit loads) over the scene's source triangles, walked per lane with a short stack. It replaces the reference's
 // uniform grid + 3D-DDA (Scene.traceRay / Grid.Iterator, src/stage3.zig:152-186, src/linalg.zig:443-497) as the
 // structure that finds the candidate triangles; the triangle test itself is the reference's
 // Triangle.rayIntersection (src/linalg.zig:696-722) — rtc_device.cuh tri_ray, the very function the grid path runs —

@@ -54,6 +54,8 @@ struct rtc_scene {
     uint32_t h_pinned_pixels = 0;
     // multi-GPU (rtc_params.num_gpus > 1): replicas of this scene on the other devices, made on first use
     std::vector<rtc_scene*> replicas;   // replicas[k] renders on its own device; owned by this scene
+    std::vector<int> multi_devices;     // the device list of the last num_gpus > 1 render (this scene's device first)
+    bool peers_enabled = false;
     cudaEvent_t ev_part = nullptr;      // "this device's part of the frame is rendered" (sample sharding: peers wait on it)
     bool is_replica = false;
     uint64_t num_tris = 0;

@@ -16,6 +16,9 @@
 
 #include <dlfcn.h>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -105,8 +108,10 @@ int rtc_scene_clone_(const rtc_scene* src, int device, rtc_scene** out)
 namespace {
 
 // The devices of an in-process multi-GPU render: the scene's own first, then the other sm_100 devices by index.
-int pick_devices(const rtc_scene* s, int n, std::vector<int>& out)
+int pick_devices(rtc_scene* s, int n, std::vector<int>& out)
 {
+    // cudaGetDeviceProperties costs milliseconds per device: the list is made once per scene and device count
+    if ((int)s->multi_devices.size() == n) { out = s->multi_devices; return RTC_OK; }
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); count = 0; }
     out.assign(1, s->device);
@@ -116,6 +121,8 @@ int pick_devices(const rtc_scene* s, int n, std::vector<int>& out)
         if (cudaGetDeviceProperties(&p, d) == cudaSuccess && p.major == 10) out.push_back(d);
     }
     if ((int)out.size() < n) return rtc_fail_(RTC_ERR_NO_DEVICE, "num_gpus = %d but only %zu sm_100 device(s) are visible", n, out.size());
+    s->multi_devices = out;
+    s->peers_enabled = false;
     return RTC_OK;
 }
 
@@ -138,8 +145,11 @@ int ensure_replicas(rtc_scene* s, const std::vector<int>& devices)
         if (int rc = rtc_scene_clone_(s, devices[g], &r)) return rc;
         s->replicas.push_back(r);
     }
-    // all pairs see each other (sample sharding reads every accumulator from every device)
-    for (int a : devices) for (int b : devices) enable_peer(a, b);
+    // all pairs see each other (sample sharding reads every accumulator from every device); once per device list
+    if (!s->peers_enabled) {
+        for (int a : devices) for (int b : devices) enable_peer(a, b);
+        s->peers_enabled = true;
+    }
     return RTC_OK;
 }
 
@@ -153,10 +163,17 @@ int rtc_render_multi_(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, 
     const uint32_t total = frame_total(p);
     if (total == 0) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "num_samples is zero");
     if (s->is_replica) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "num_gpus > 1 on a replica");
+    // RTC_TRACE_MULTI=1: host-side phase times of this call on stderr
+    static const bool trace = getenv("RTC_TRACE_MULTI") && getenv("RTC_TRACE_MULTI")[0] == '1';
+    const auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (trace) fprintf(stderr, "rtc multi: %-22s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
+    };
     std::vector<int> devices;
     if (int rc = pick_devices(s, N, devices)) return rc;
     if (p->accel == RTC_ACCEL_BVH && !s->has_bvh) { if (int rc = rtc_scene_build_bvh(s, 0, nullptr)) return rc; }
     if (int rc = ensure_replicas(s, devices)) return rc;
+    lap("devices + replicas");
     std::vector<rtc_scene*> sc(N);
     sc[0] = s;
     for (int g = 1; g < N; ++g) sc[g] = s->replicas[g - 1];
@@ -248,9 +265,11 @@ int rtc_render_multi_(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, 
             CU(cudaStreamSynchronize(sc[g]->stream));
         }
     }
+    lap("parts rendered + fetched");
     rtc_params all = *p;
     all.tile_world = 0; all.tile_rank = 0;
     rtc_copy_out_(cam, &all, hf, rgb_out, aux, want_hits);
+    lap("copied to the caller");
     if (want_stats) {
         rtc_stats sum;
         memset(&sum, 0, sizeof sum);

@@ -381,9 +381,9 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
 // k_trace_bvh: Scene.traceRay (src/stage3.zig:152-186) over a ray queue with the 8-wide BVH of rtc_bvh.cuh in
 // place of the grid (RTC_ACCEL_BVH). Persistent warps with the same per-lane refill as k_trace. One round:
 //   A  every live lane pops the nearest pending child of its own ray and tests that node's eight quantised boxes
-//      (one 80-byte node = five 128-bit loads; the lanes of a warp run this part converged);
+//      (one 80-byte node at a 96-byte stride = three sector-aligned 256-bit loads; the lanes run this part converged);
 //   B  the triangles of the leaves that were hit — a few per lane, none for most — are POOLED over the warp and
-//      dealt out one (ray, triangle) pair per lane per pass (48-byte records, three 128-bit loads, the reference's
+//      dealt out one (ray, triangle) pair per lane per pass (48-byte records at a 64-byte stride, two 256-bit loads, the reference's
 //      Triangle.rayIntersection). Tested per lane they ran at 3.5 of 32 lanes (profiles/r2b_*). Winner per ray =
 //      atomicMin on (t bits << 32 | source id) in shared memory: smallest t > 0, smaller source id on exact ties;
 //   C  owners fold their winner in (strictly nearer, or equal and smaller source id) and pop their stack.
