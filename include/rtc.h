@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 8u
+#define RTC_ABI_VERSION 9u
 
 typedef enum rtc_status {
     RTC_OK = 0,
@@ -243,6 +243,11 @@ void rtc_comm_destroy(rtc_comm* comm);
  * not filled by this entry point. */
 int  rtc_render_sharded(rtc_scene* scene, rtc_comm* comm, const rtc_camera* camera, const rtc_params* params,
                         uint8_t* rgb_out, rtc_aux* aux);
+
+/* What the first rtc_render with num_gpus = N (and / or accel) would do before it renders, ahead of time: CUDA contexts
+ * on the other devices, the scene's replicas there (peer copies), peer access, the BVH. A host that brackets its render
+ * phase (the reference's "Rendered in", src/main.zig:125-127) calls this in its "Compiled in" phase; optional. */
+int  rtc_scene_prepare_gpus(rtc_scene* scene, int num_gpus, uint32_t accel);
 
 /* Makes `stream` (a cudaStream_t; NULL = back to the scene's own stream) the stream every later call on this scene
  * launches on — a host that brackets frames with its own CUDA events, or orders them against its own work, passes its

@@ -45,6 +45,11 @@ def test_num_gpus_beyond_the_box_is_an_error(setup):
     with pytest.raises(rtc.RtcError) as e:
         scene.render(cam, rtc.make_params(num_samples=2, num_gpus=n))
     assert e.value.code == abi.RTC_ERR_NO_DEVICE
+    with pytest.raises(rtc.RtcError) as e:
+        scene.prepare_gpus(n)
+    assert e.value.code == abi.RTC_ERR_NO_DEVICE
+    scene.prepare_gpus(1, abi.RTC_ACCEL_BVH)                # one device: builds the BVH, nothing else
+    assert scene.build_bvh()["num_tris"] == len(np.unique(geo.tri_data["src_tri"]))
     with pytest.raises(rtc.RtcError) as e:                  # sharding fields and num_gpus exclude each other
         scene.render(cam, rtc.make_params(num_samples=2, num_gpus=2, tile_rank=0, tile_world=2))
     assert e.value.code == abi.RTC_ERR_INVALID_ARGUMENT
@@ -56,6 +61,7 @@ def test_inprocess_strips_equal_one_gpu(orc, setup, accel):
         pytest.skip("needs 2 GPUs")
     spec, geo, scene, cam = setup
     n = min(_ngpu(), 4)
+    scene.prepare_gpus(n, accel)                            # replicas ahead of the first render (idempotent)
     one = scene.render(cam, rtc.make_params(num_samples=6, seed=3, accel=accel), want_radiance=True, want_stats=True, instrumented=False)
     many = scene.render(cam, rtc.make_params(num_samples=6, seed=3, accel=accel, num_gpus=n, shard=abi.RTC_SHARD_STRIPS),
                         want_radiance=True, want_stats=True, instrumented=False)

@@ -57,7 +57,9 @@ def main():
         ("profiles/r2e_bench_inproc2.json", "cfg3 2 GPUs strong, ONE process: rtc_render(num_gpus=2), host clock incl. D2H"),
         ("profiles/r2_n8_cfg3_strips.json", "cfg3 8 GPUs strong, strips"),
         ("profiles/r2_n8_cfg3_samples.json", "cfg3 8 GPUs strong, sample ranges"),
-        ("profiles/r2_n8_cfg3_inproc.json", "cfg3 8 GPUs strong, ONE process: rtc_render(num_gpus=8)"),
+        ("profiles/r2_n8_cfg3_inproc.json", "cfg3 8 GPUs strong, ONE process: rtc_render(num_gpus=8), strips, host clock incl. D2H + host copy"),
+        ("profiles/r2_n8_cfg3_inproc_samples.json", "cfg3 8 GPUs strong, ONE process: rtc_render(num_gpus=8), sample ranges combined over NVLink peer loads"),
+        ("profiles/r2n_inproc4.json", "cfg3 4 GPUs strong, ONE process: rtc_render(num_gpus=4), strips"),
         ("profiles/r2_n8_cfg4_strips.json", "cfg4 (5 M triangles, 4K, 256 spp) 8 GPUs strong, strips, BVH"),
     ]:
         row = bench_row(rel, label)

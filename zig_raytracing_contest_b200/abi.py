@@ -5,7 +5,7 @@ Each class names the rtc.h struct it mirrors; rtc.h in turn cites the reference 
 """
 import ctypes as C
 
-RTC_ABI_VERSION = 8
+RTC_ABI_VERSION = 9
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARGUMENT = 1
@@ -142,7 +142,7 @@ class HostScene(C.Structure):     # rtc_host_scene
 # Every symbol include/rtc.h declares (checked by tests/test_abi.py against the built library).
 EXPORTED_SYMBOLS = [
     "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
-    "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_scene_set_stream",
+    "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_scene_set_stream", "rtc_scene_prepare_gpus",
     "rtc_comm_unique_id", "rtc_comm_create", "rtc_comm_destroy", "rtc_render_sharded", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_geometry_build_device", "rtc_scene_create_from_soup",
     "rtc_scene_create_from_gltf", "rtc_gltf_load_device",

@@ -194,6 +194,12 @@ int main(int argc, char** argv)
     fprintf(stderr, "info: Unique triangle count: %u/%llu (%.2f%%)\n", bi.num_src_tris, (unsigned long long)bi.num_tris,
             bi.num_tris ? 100.0 * bi.num_src_tris / (double)bi.num_tris : 0.0);
 
+    if (args.gpus > 1 || args.accel == RTC_ACCEL_BVH) {
+        // set-up that belongs to "Compiled", not to "Rendered": contexts + replicas on the other devices, the BVH
+        t = Clock::now();
+        if (rtc_scene_prepare_gpus(scene, args.gpus, args.accel) != RTC_OK) return die("prepare");
+        fprintf(stderr, "info: Prepared %d device(s)%s in %s\n", args.gpus, args.accel == RTC_ACCEL_BVH ? " + BVH" : "", since(t).c_str());
+    }
     std::vector<uint8_t> img((size_t)camera.w * camera.h * 3);
     t = Clock::now();
     rtc_params prm;

@@ -400,6 +400,18 @@ void rtc_comm_destroy(rtc_comm* c)
     delete c;
 }
 
+int rtc_scene_prepare_gpus(rtc_scene* s, int num_gpus, uint32_t accel)
+{
+    if (!s) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "null scene");
+    if (num_gpus < 0 || num_gpus > RTC_MAX_GPUS) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "num_gpus %d outside 0..%d", num_gpus, RTC_MAX_GPUS);
+    if (s->is_replica) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "rtc_scene_prepare_gpus on a replica");
+    if (accel == RTC_ACCEL_BVH && !s->has_bvh) { if (int rc = rtc_scene_build_bvh(s, 0, nullptr)) return rc; }
+    if (num_gpus <= 1) return RTC_OK;
+    std::vector<int> devices;
+    if (int rc = pick_devices(s, num_gpus, devices)) return rc;
+    return ensure_replicas(s, devices);
+}
+
 int rtc_scene_set_stream(rtc_scene* s, void* stream)
 {
     if (!s) return rtc_fail_(RTC_ERR_INVALID_ARGUMENT, "null scene");

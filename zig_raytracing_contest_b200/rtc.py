@@ -51,6 +51,7 @@ def lib():
     L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
     L.rtc_scene_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.BvhInfo)]
     L.rtc_scene_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    L.rtc_scene_prepare_gpus.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
     L.rtc_comm_unique_id.argtypes = [C.c_void_p]
     L.rtc_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.rtc_comm_destroy.argtypes = [C.c_void_p]
@@ -399,6 +400,10 @@ class Scene:
         if want_stats:
             out["stats"] = st.as_dict()
         return out
+
+    def prepare_gpus(self, num_gpus, accel=abi.RTC_ACCEL_GRID):
+        """Replicas on the other devices (and the BVH) ahead of the first render that needs them."""
+        _check(lib().rtc_scene_prepare_gpus(self._h, int(num_gpus), int(accel)))
 
     def set_stream(self, stream_ptr=None):
         """Every later call on this scene launches on this cudaStream_t (None: back to the scene's own stream)."""
