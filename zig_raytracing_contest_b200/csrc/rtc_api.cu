@@ -379,18 +379,25 @@ Shard shard_pixels(const rtc_camera* cam, const rtc_params* p)
 }
 
 // Wavefront scratch for `slots` path slots and `levels` scattering levels (rtc_device.cuh WaveScratch).
-// The slot count is capped by a byte budget (RTC_WAVE_BYTES, default 6 GiB, at most half of the free HBM);
-// frames with more paths than slots are rendered in batches.
+// The slot count is capped by a byte budget; frames with more paths than slots are rendered in batches. The budget has
+// two stages: 6 GiB for a scene's FIRST frame (a one-shot program does not pay a 30 GB allocation inside its render
+// bracket), 48 GiB from the second frame on when the first one had to be batched (a render loop amortises the
+// allocation: cfg3 in one batch and 11 launches instead of 6.4 batches and 61 launches, +1.8 %, profiles/r2p_*).
+// Always at most half of the free HBM; RTC_WAVE_BYTES fixes it for both stages. Batching never changes a result.
 int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels)
 {
     if (levels < 1) levels = 1;
+    const char* env = getenv("RTC_WAVE_BYTES");
+    const long long env_bytes = env ? atoll(env) : 0;
+    const int stage = s->render_calls >= 1 ? 1 : 0;
+    const bool grow = env_bytes <= 0 && s->wave_budget_limited && stage > s->wave_stage;
     // fast path: the scratch already holds this frame, or is already as large as the budget allowed
-    if (s->wave.cap && s->wave.max_levels >= levels &&
+    if (!grow && s->wave.cap && s->wave.max_levels >= levels &&
         (s->wave.cap >= pixels * (uint64_t)samples || (s->wave_budget_limited && s->wave.max_levels == levels)))
         return RTC_OK;
     const size_t per_slot = 2 * 64 + sizeof(uint2) + sizeof(float4) + (size_t)levels * (sizeof(float4) + sizeof(float2));
-    size_t budget = (size_t)6 << 30;
-    if (const char* env = getenv("RTC_WAVE_BYTES")) { const long long v = atoll(env); if (v > 0) budget = (size_t)v; }
+    size_t budget = stage ? (size_t)48 << 30 : (size_t)6 << 30;
+    if (env_bytes > 0) budget = (size_t)env_bytes;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
         size_t held = 0;
@@ -403,7 +410,7 @@ int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels
     if (want > fit) want = fit;
     if (want > 0x7FFFFFFFull) want = 0x7FFFFFFFull;
     if (want < 1024) want = 1024;
-    if (s->wave.cap >= want && s->wave.max_levels >= levels) return RTC_OK;
+    if (s->wave.cap >= want && s->wave.max_levels >= levels) { s->wave_stage = stage; return RTC_OK; }
     for (void* p : s->wave_allocs) cudaFree(p);
     s->wave_allocs.clear();
     s->wave = rtc::WaveScratch{};
@@ -428,6 +435,7 @@ int ensure_wave(rtc_scene* s, uint64_t pixels, uint32_t samples, uint32_t levels
     w.cap = (uint32_t)cap; w.max_levels = levels;
     s->wave = w;
     s->wave_budget_limited = limited;
+    s->wave_stage = stage;
     return RTC_OK;
 }
 
@@ -457,6 +465,7 @@ int launch_render(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, floa
         : rtc::exact::launch_render(dev, dc, dp, primary, accum, pout, s->counters, s->wave, cfg, &launches, bvh);
     s->launches += launches;
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    s->render_calls += 1;
     return RTC_OK;
 }
 

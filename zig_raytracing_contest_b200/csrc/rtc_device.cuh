@@ -250,8 +250,21 @@ __device__ __forceinline__ TexTaps tex_taps(const DevTexture& tx, float u, float
     t.fu = fracf_(u); t.fv = fracf_(v);
     return t;
 }
+// A 1x1 texture (the dummy textures of materials without an image, src/stage1.zig:411-425 — most emissive and
+// transparency textures): all four taps are the one texel a, and with finite a, u, v both lerps are fma(+0, f, a) with
+// f = |frac| >= 0, i.e. a + (+0) — the value returned here, bit for bit (-0 becomes +0 on both routes). Anything
+// non-finite takes the general route, which makes the reference's NaN.
+__device__ __forceinline__ bool tex_is_const(const DevTexture& tx, float u, float v)
+{
+    return (tx.w | tx.h) == 1 && fabsf(u) < __int_as_float(0x7f800000) && fabsf(v) < __int_as_float(0x7f800000);
+}
 __device__ __forceinline__ v3 tex_sample3(const DevTexture& tx, float u, float v)
 {
+    if (tex_is_const(tx, u, v)) {
+        const float4 a = __ldg((const float4*)tx.texels);
+        const float big = __int_as_float(0x7f800000);
+        if (fabsf(a.x) < big && fabsf(a.y) < big && fabsf(a.z) < big) return mk(a.x + 0.0f, a.y + 0.0f, a.z + 0.0f);
+    }
     const TexTaps t = tex_taps(tx, u, v);
     const float4* p = (const float4*)tx.texels;
     const float4 a = __ldg(p + t.i11), b = __ldg(p + t.i21), c = __ldg(p + t.i12), d = __ldg(p + t.i22);
@@ -261,6 +274,10 @@ __device__ __forceinline__ v3 tex_sample3(const DevTexture& tx, float u, float v
 }
 __device__ __forceinline__ float tex_sample1(const DevTexture& tx, float u, float v)
 {
+    if (tex_is_const(tx, u, v)) {
+        const float a = __ldg((const float*)tx.texels);
+        if (fabsf(a) < __int_as_float(0x7f800000)) return a + 0.0f;
+    }
     const TexTaps t = tex_taps(tx, u, v);
     const float* p = (const float*)tx.texels;
     const float a = __ldg(p + t.i11), b = __ldg(p + t.i21), c = __ldg(p + t.i12), d = __ldg(p + t.i22);

@@ -64,6 +64,8 @@ struct rtc_scene {
     rtc::WaveScratch wave{};
     std::vector<void*> wave_allocs;
     bool wave_budget_limited = false;
+    int wave_stage = 0;                 // budget stage the scratch was sized with (0: first frame, 1: render loop)
+    uint64_t render_calls = 0;          // frames (parts) launched on this scene so far
     uint64_t launches = 0;
     std::vector<cudaEvent_t> timer_events;
     rtc::TraceTimer timer{};
