@@ -66,7 +66,9 @@ def main():
         if row:
             runs.append(row)
     sweep = []
-    for rel in sorted(glob.glob(os.path.join(ROOT, "profiles", "r2*_cfg5_n*.json"))):
+    # the latest sweep (r2u: final kernels and scratch policy); the earlier one (r2h / r2i) stays under profiles/ as history
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r2u_cfg5_n*.json"))) or sorted(glob.glob(os.path.join(ROOT, "profiles", "r2[hi]_cfg5_n*.json")))
+    for rel in files:
         d = load(os.path.relpath(rel, ROOT))
         if not d:
             continue
@@ -90,8 +92,10 @@ def main():
         "runs": runs,
         "cfg5_spp_sweep": {"workload": "5 M-triangle terrain, 3840x2160, max_bounce 4; one fixed frame sharded over the GPUs by sample ranges, "
                                        "rgb accumulators combined by ncclReduce inside librtc.so (rtc_render_sharded)",
-                           "what_bends_the_curve": "combine_and_gaps_ms (reduce of 99.5 MB + resolve + launch gaps) is 0.5-0.9 ms at every N: "
-                                                   "visible only where a frame takes < 20 ms (16 spp at N >= 4); the e2e column adds the 24.9 MB D2H + host copy (3-4 ms)",
+                           "what_bends_the_curve": "combine_and_gaps_ms (ncclReduce of 99.5 MB of rgb sums + resolve + launch gaps) is 0.5-0.8 ms at every N and "
+                                                   "every spp: 6.7 % of the 9.3 ms frame at 16 spp on 8 GPUs, 0.4 % at 256 spp; the rest of the loss at 16 spp on 8 GPUs is the "
+                                                   "render itself at 2 spp per rank (kernel tails and launch gaps of 11 launches over 8.7 ms); the e2e column adds the 24.9 MB D2H "
+                                                   "+ host copy on rank 0 (3 ms)",
                            "rows": sweep},
         "counters": load("profiles/counters.json"),
         "round1_runs": r1,

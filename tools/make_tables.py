@@ -25,7 +25,7 @@ def main():
     sw = m["cfg5_spp_sweep"]["rows"]
     lines += ["", "cfg5 — spp sweep at 3840×2160 on the 5 M-triangle scene, ONE fixed frame sharded by sample ranges, rgb accumulators combined by `ncclReduce` inside "
               "`librtc.so` (`tools/cfg5_sweep.py`; ms per frame on the device, max over ranks; in brackets the strong-scaling efficiency against the same row at 1 GPU; "
-              "`profiles/r2h_cfg5_n1.json`, `r2i_cfg5_n{2,4,8}.json`):", "",
+              "`profiles/r2u_cfg5_n{1,2,4,8}.json`; the same sweep with the kernels of three commits earlier: `r2h_cfg5_n1.json`, `r2i_cfg5_n{2,4,8}.json`):", "",
               "| path | spp | 1 GPU | 2 GPUs | 4 GPUs | 8 GPUs | 8 GPUs: Mrays/s | combine + gaps at 8 | e2e at 8 (host frame out) |", "|---|---|---|---|---|---|---|---|---|"]
     for accel in ("bvh", "grid"):
         for spp in sorted({r["spp_total"] for r in sw if r["accel"] == accel}):
