@@ -234,7 +234,7 @@ def roofline(name, accel_key, cs, trace_ms, trace_launches, kern_ms, algo_bytes,
 def run_gpu(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from zig_raytracing_contest_b200 import abi, rtc
+    from zig_raytracing_contest_b200 import abi, rtc, shard
     if rtc.device_count() < 1:
         raise SystemExit("bench.py: no sm_100 GPU visible and the render path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -272,9 +272,7 @@ def run_gpu(args, rank, world, local_rank):
     comm = None
     if world > 1:
         # the library's own NCCL communicator; torch.distributed only hands the id around
-        box = [rtc.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        comm = rtc.Comm(box[0], rank, world, device=local_rank)
+        comm = rtc.Comm(shard.broadcast_comm_id(rtc.comm_unique_id), rank, world, device=local_rank)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     # the library launches on the stream the events are recorded on: a stream of this process, handed to the scene
     stream = torch.cuda.Stream(device=dev)

@@ -89,6 +89,17 @@ def _worker(rank, world, port, out_dir):
     for a, b in shard.strips_of(rank, world, cam.h, 9):
         strided[a:b] = torch.from_numpy(oracle.render(desc, cam, full_prm, num_threads=1, rows=(a, b))["rgb"][a:b].copy())
     frame3 = shard.gather_strips(strided, 9, dst=0)
+    # what bench.py / tools/cfg5_sweep.py ask of torch.distributed at N > 1: the library's communicator id from rank 0 to
+    # every rank (made by librtc.so's run-time-loaded NCCL when that loads here, else a stand-in), and a max over ranks
+    def make_id():
+        try:
+            return rtc.comm_unique_id()
+        except (rtc.RtcError, ImportError, OSError):
+            return bytes(range(128))
+    cid = shard.broadcast_comm_id(make_id, src=0)
+    slowest = shard.max_over_ranks(10.0 + rank)
+    np.save(os.path.join(out_dir, "cid%d.npy" % rank), np.frombuffer(cid, np.uint8))
+    np.save(os.path.join(out_dir, "max%d.npy" % rank), np.array([slowest]))
     if rank == 0:
         ref = oracle.render(desc, cam, full_prm, num_threads=1)
         np.save(os.path.join(out_dir, "acc.npy"), acc.numpy())
@@ -111,3 +122,6 @@ def test_two_ranks_reproduce_the_single_frame(tmp_path, orc):
     assert np.array_equal(np.load(tmp_path / "frame.npy"), np.load(tmp_path / "ref_rgb.npy"))
     assert np.array_equal(np.load(tmp_path / "frame2.npy"), np.load(tmp_path / "ref_rgb.npy"))
     assert np.array_equal(np.load(tmp_path / "frame3.npy"), np.load(tmp_path / "ref_rgb.npy"))
+    ids = [np.load(tmp_path / ("cid%d.npy" % r)) for r in range(world)]
+    assert ids[0].shape == (128,) and np.array_equal(ids[0], ids[1])         # every rank holds rank 0's communicator id
+    assert [float(np.load(tmp_path / ("max%d.npy" % r))[0]) for r in range(world)] == [11.0, 11.0]

@@ -33,7 +33,7 @@ def main():
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
-    from zig_raytracing_contest_b200 import abi, rtc, scenes
+    from zig_raytracing_contest_b200 import abi, rtc, scenes, shard
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -47,9 +47,7 @@ def main():
     cam = spec.camera(height=args.height)
     comm = None
     if world > 1:
-        box = [rtc.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        comm = rtc.Comm(box[0], rank, world, device=local)
+        comm = rtc.Comm(shard.broadcast_comm_id(rtc.comm_unique_id), rank, world, device=local)
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     scene.set_stream(stream.cuda_stream)
@@ -78,11 +76,11 @@ def main():
                                                     shard=abi.RTC_SHARD_STRIPS if args.strips else abi.RTC_SHARD_SAMPLES),
                          img=img if rank == 0 else None, to_host=True)
     rows = []
-    shard = abi.RTC_SHARD_STRIPS if args.strips else abi.RTC_SHARD_SAMPLES
+    shard_mode = abi.RTC_SHARD_STRIPS if args.strips else abi.RTC_SHARD_SAMPLES
     plan = [("bvh", s) for s in args.spp] + [("grid", s) for s in args.grid_spp]
     for accel_name, spp in plan:
         accel = abi.RTC_ACCEL_BVH if accel_name == "bvh" else abi.RTC_ACCEL_GRID
-        prm = rtc.make_params(num_samples=spp, max_bounce=4, seed=1, accel=accel, shard=shard, tile_rows=8)
+        prm = rtc.make_params(num_samples=spp, max_bounce=4, seed=1, accel=accel, shard=shard_mode, tile_rows=8)
         if spp <= 256:
             scene.render_sharded(comm, cam, prm, to_host=False)
         barrier()

@@ -100,3 +100,25 @@ def gather_strips(frame, rows, dst=0, group=None):
         n_r = len(range(r, nstrips, world))
         view[r::world] = out[r][:n_r]
     return padded[:H]
+
+
+def broadcast_comm_id(make_id, src=0, group=None):
+    """The library's NCCL communicator (rtc_comm_create) needs the same 128-byte id on every rank: rank `src` makes it
+    (make_id = rtc.comm_unique_id) and torch.distributed — whatever its backend — hands the bytes around. This is all
+    the host framework contributes to the data path of a sharded frame; the collective itself is issued by librtc.so."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return make_id()
+    box = [make_id() if dist.get_rank(group) == src else None]
+    dist.broadcast_object_list(box, src=src, group=group)
+    if not isinstance(box[0], (bytes, bytearray)) or len(box[0]) != 128:
+        raise RuntimeError("communicator id did not arrive (%r)" % type(box[0]))
+    return bytes(box[0])
+
+
+def max_over_ranks(value, device=None, group=None):
+    """A timing as the contract wants it: the MAX over the ranks (float in, float out)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return float(t[0])
