@@ -263,6 +263,23 @@ int  rtc_scene_set_stream(rtc_scene* scene, void* stream);
 int rtc_render_accumulate(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
                           void* d_accum, void* stream);
 
+/* rtc_render_accumulate for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and bit-identical sums, but the wavefront scratch (ray queues, hit records, throughput
+ * stacks, queue counters) is a static device array of RTC_STATIC_SCRATCH_BYTES inside librtc.so — every GPU that loads
+ * the library holds those bytes until the process exits — and the call makes no cudaMalloc / cudaFree / allocating
+ * library call. The caller passes the inputs (scene, camera, params) and the output (d_accum, device, w*h float4).
+ * Limit: this call's paths = (pixels of the call's band or strips) x num_samples must fit the array in ONE batch at
+ * 152 + 24 * max_bounce bytes per path: 270 k paths at max_bounce 4 (e.g. 256 x 256 at 4 samples), 39 k at max_bounce 64;
+ * more -> RTC_ERR_UNSUPPORTED with the numbers in rtc_last_error(), nothing rendered (split the frame with
+ * tile_rank / tile_world or sample_offset, or use rtc_render_accumulate). RTC_ACCEL_BVH needs rtc_scene_build_bvh to
+ * have run (the build allocates); num_gpus > 1 is rejected. The array is shared by EVERY scene and every call on a
+ * device and keeps the last call's contents (the call clears the part that must start at zero, on `stream`): calls
+ * that overlap on one GPU — two streams, two scenes, two threads — race; order them on one stream or with events. */
+#define RTC_STATIC_SCRATCH_BYTES (64u << 20)
+int rtc_render_accumulate_static(rtc_scene* scene, const rtc_camera* camera, const rtc_params* params,
+                                 void* d_accum, void* stream);
+
 /* pixel.mul(inv_num_samples).toRGB() (src/stage3.zig:242, src/linalg.zig:150-159):
  * d_accum (w*h float4) -> d_rgb (w*h*3 bytes) and/or d_radiance (w*h*3 floats). */
 int rtc_resolve(const void* d_accum, uint32_t num_pixels, uint32_t total_samples,

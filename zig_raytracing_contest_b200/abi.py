@@ -23,6 +23,7 @@ RTC_ACCEL_BVH = 1
 RTC_SHARD_STRIPS = 0
 RTC_SHARD_SAMPLES = 1
 RTC_MAX_GPUS = 16
+RTC_STATIC_SCRATCH_BYTES = 64 << 20       # rtc_render_accumulate_static's static device array
 RTC_COMM_ID_BYTES = 128
 RTC_MATH_EXACT = 0
 RTC_MATH_FAST = 1
@@ -141,7 +142,7 @@ class HostScene(C.Structure):     # rtc_host_scene
 
 # Every symbol include/rtc.h declares (checked by tests/test_abi.py against the built library).
 EXPORTED_SYMBOLS = [
-    "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate",
+    "rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_accumulate", "rtc_render_accumulate_static",
     "rtc_resolve", "rtc_scene_stats", "rtc_scene_build_bvh", "rtc_scene_set_stream", "rtc_scene_prepare_gpus",
     "rtc_comm_unique_id", "rtc_comm_create", "rtc_comm_destroy", "rtc_render_sharded", "rtc_geometry_build", "rtc_geometry_free",
     "rtc_geometry_build_device", "rtc_scene_create_from_soup",

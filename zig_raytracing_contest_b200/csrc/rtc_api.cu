@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -730,6 +731,120 @@ int rtc_scene_stats(rtc_scene* s, rtc_stats* out)
         out->hits_shaded += st.hits_shaded; out->paths += st.paths; out->launches += st.launches;
         out->trace_ms += st.trace_ms; out->trace_launches += st.trace_launches; out->trace_launches_untimed += st.trace_launches_untimed;
     }
+    return RTC_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// rtc_render_accumulate_static: rtc_render_accumulate with the wavefront scratch (ray queues, hit records, throughput
+// stacks, queue counters) in a file-scope device array instead of cudaMalloc'd memory — for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid it). No counterpart in the reference.
+// Nothing on this path calls cudaMalloc / cudaFree / an allocating library routine.
+//
+// g_static_scratch below is, in HOST code, a stand-in for the symbol and not a device address: the device address is
+// taken once per device with cudaGetSymbolAddress (that device current) and only that pointer goes to the kernels.
+// Every GPU that loads the library holds the array until exit. All calls share it, and it keeps the last call's
+// contents: the only part that must start at zero (the queue counters) is cleared on the caller's stream by the
+// launcher before every batch; the rest is written before it is read. Calls that overlap on a GPU race.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[RTC_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+struct StaticScratchAddr { bool known = false; unsigned char* ptr = nullptr; };
+StaticScratchAddr g_static_addr[RTC_MAX_GPUS];
+std::mutex g_static_mu;
+
+constexpr size_t kStaticAlign = 256;
+constexpr size_t kStaticCountsBytes = 2 * (rtc::kMaxBounce + 1) * sizeof(uint32_t);
+constexpr size_t kStaticSections = 13;      // 8 queue planes, hits, stack_e, stack_a, leaf, counts
+
+size_t static_slot_bytes(uint32_t levels)
+{
+    return 2 * 64 + sizeof(uint2) + sizeof(float4) + (size_t)levels * (sizeof(float4) + sizeof(float2));
+}
+
+// device address of g_static_scratch on `device` (which is current): asked for once per device
+int static_scratch_base(int device, unsigned char** out)
+{
+    if (device < 0 || device >= RTC_MAX_GPUS) return fail(RTC_ERR_INVALID_ARGUMENT, "device %d outside [0, %d)", device, RTC_MAX_GPUS);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    StaticScratchAddr& a = g_static_addr[device];
+    if (!a.known) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(RTC_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", device, cudaGetErrorString(e));
+        }
+        a.ptr = (unsigned char*)p;
+        a.known = true;
+    }
+    *out = a.ptr;
+    return RTC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtc_render_accumulate_static(rtc_scene* s, const rtc_camera* cam, const rtc_params* p, void* d_accum, void* stream)
+{
+    if (int rc = check_render_args(s, cam, p)) return rc;
+    if (!d_accum) return fail(RTC_ERR_INVALID_ARGUMENT, "d_accum is null");
+    if (p->num_gpus > 1) return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_render_accumulate_static renders on the scene's device only (num_gpus %d)", (int)p->num_gpus);
+    const bool primary = p->mode == RTC_MODE_PRIMARY;
+    if (p->accel == RTC_ACCEL_BVH && !s->has_bvh)
+        return fail(RTC_ERR_INVALID_ARGUMENT, "rtc_render_accumulate_static allocates nothing: call rtc_scene_build_bvh before asking for RTC_ACCEL_BVH");
+    const Shard sh = shard_pixels(cam, p);
+    const uint32_t samples = primary ? 1u : p->num_samples;
+    const uint32_t levels = primary ? 1u : (p->max_bounce < 1 ? 1u : p->max_bounce);
+    const uint64_t paths = (uint64_t)sh.count * samples;
+    const size_t usable = (size_t)RTC_STATIC_SCRATCH_BYTES - kStaticCountsBytes - kStaticSections * kStaticAlign;
+    const uint64_t cap = usable / static_slot_bytes(levels);
+    if (paths > cap)
+        return fail(RTC_ERR_UNSUPPORTED, "rtc_render_accumulate_static: %llu paths (%u pixels x %u samples) exceed the %llu that the %u MiB static scratch "
+                    "holds at max_bounce %u (%zu bytes per path); render fewer pixels or samples per call, or use rtc_render_accumulate",
+                    (unsigned long long)paths, sh.count, samples, (unsigned long long)cap, (unsigned)(RTC_STATIC_SCRATCH_BYTES >> 20), levels,
+                    static_slot_bytes(levels));
+    if (paths == 0) return RTC_OK;
+    DeviceGuard guard(s->device);
+    unsigned char* base = nullptr;
+    if (int rc = static_scratch_base(s->device, &base)) return rc;
+    // carve the sections (rtc_device.cuh WaveScratch), each 256-byte aligned
+    size_t off = 0;
+    auto take = [&](size_t bytes) { unsigned char* q = base + off; off += (bytes + kStaticAlign - 1) / kStaticAlign * kStaticAlign; return q; };
+    const size_t n = (size_t)cap;
+    rtc::WaveScratch w{};
+    for (int k = 0; k < 2; ++k) {
+        w.q[k].a0 = (float4*)take(n * sizeof(float4)); w.q[k].a1 = (float4*)take(n * sizeof(float4));
+        w.q[k].a2 = (float4*)take(n * sizeof(float4)); w.q[k].a3 = (float4*)take(n * sizeof(float4));
+    }
+    w.hits = (uint2*)take(n * sizeof(uint2));
+    w.stack_e = (float4*)take(n * levels * sizeof(float4));
+    w.stack_a = (float2*)take(n * levels * sizeof(float2));
+    w.leaf = (float4*)take(n * sizeof(float4));
+    w.counts = (uint32_t*)take(kStaticCountsBytes);
+    if (off > (size_t)RTC_STATIC_SCRATCH_BYTES) return fail(RTC_ERR_CUDA, "static scratch layout: %zu bytes > %zu", off, (size_t)RTC_STATIC_SCRATCH_BYTES);
+    w.cap = (uint32_t)cap; w.max_levels = levels;
+
+    rtc::DevParams dp;
+    dp.num_samples = p->num_samples; dp.max_bounce = p->max_bounce; dp.sample_offset = p->sample_offset;
+    dp.seed_lo = (uint32_t)p->seed; dp.seed_hi = (uint32_t)(p->seed >> 32);
+    dp.first_pixel = sh.first; dp.num_pixels = sh.count; dp.strip_px = sh.strip_px; dp.stride_px = sh.stride_px;
+    const rtc::DevCamera dc = to_dev(*cam);
+    rtc::LaunchCfg cfg; cfg.sm_count = s->sm_count; cfg.stream = (cudaStream_t)stream; cfg.stats = p->collect_stats != 0;
+    cfg.timer = nullptr;                       // no event brackets on this path
+    cfg.cache = &s->cache;
+    rtc::PrimaryOut pout; pout.hit_id = nullptr; pout.hit_tuv = nullptr;
+    uint32_t launches = 0;
+    const rtc::BvhView* bvh = p->accel == RTC_ACCEL_BVH ? &s->bvh : nullptr;
+    const cudaError_t e = p->math == RTC_MATH_FAST
+        ? rtc::fast::launch_render(s->dev, dc, dp, primary, (float4*)d_accum, pout, s->counters, w, cfg, &launches, bvh)
+        : rtc::exact::launch_render(s->dev, dc, dp, primary, (float4*)d_accum, pout, s->counters, w, cfg, &launches, bvh);
+    s->launches += launches;
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     return RTC_OK;
 }
 

@@ -47,6 +47,8 @@ def lib():
                              C.POINTER(abi.Aux)]
     L.rtc_render_accumulate.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Params),
                                         C.c_void_p, C.c_void_p]
+    L.rtc_render_accumulate_static.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Params),
+                                               C.c_void_p, C.c_void_p]
     L.rtc_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.rtc_scene_stats.argtypes = [C.c_void_p, C.POINTER(abi.Stats)]
     L.rtc_scene_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.BvhInfo)]
@@ -413,6 +415,12 @@ class Scene:
         """Adds params.num_samples samples per pixel into a device float4 accumulator (async)."""
         _check(lib().rtc_render_accumulate(self._h, C.byref(camera), C.byref(params),
                                            C.c_void_p(d_accum_ptr), C.c_void_p(stream_ptr or 0)))
+
+    def render_accumulate_static(self, camera, params, d_accum_ptr, stream_ptr=None):
+        """render_accumulate with the wavefront scratch in librtc.so's static device array: allocates nothing; at most
+        abi.RTC_STATIC_SCRATCH_BYTES / (152 + 24 * max_bounce) paths per call (rtc_render_accumulate_static)."""
+        _check(lib().rtc_render_accumulate_static(self._h, C.byref(camera), C.byref(params),
+                                                  C.c_void_p(d_accum_ptr), C.c_void_p(stream_ptr or 0)))
 
     def build_bvh(self, num_threads=0):
         """RTC_ACCEL_BVH's structure, ahead of the first render that asks for it (rtc_scene_build_bvh)."""
