@@ -111,6 +111,22 @@ RTC_HD void bvh_ray_init(BvhRay& r, v3 o, v3 d)
     r.octinv4 = (7u ^ oct) * 0x01010101u;
 }
 
+// Byte j of w as a float. RTC_BVH_CVT = 0: the conversion instruction (I2F.U8 with its byte selector: one issue slot, on
+// the conversion pipe); 1: one byte permute into the mantissa of 2^23 and one FADD (exact: 2^23 + q - 2^23 = q; two
+// issue slots on the ALU and FMA pipes); 2: kept for A/B — the far planes by permute, the near planes by conversion.
+#ifndef RTC_BVH_CVT
+#define RTC_BVH_CVT 0
+#endif
+RTC_HD float bvh_byte_f(uint32_t w, int j, bool far_plane)
+{
+#if defined(__CUDA_ARCH__) && RTC_BVH_CVT
+    if (RTC_BVH_CVT == 1 || far_plane)
+        return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u | (uint32_t)j)) - 8388608.0f;
+#endif
+    (void)far_plane;
+    return (float)((w >> (8 * j)) & 0xFFu);
+}
+
 // Slab test of the ray against the (up to) eight quantised child boxes of node ni, clipped to [0, tmax]. Fills the
 // node group {child_base, inner hits << 24 | imask} and the triangle group {tri_base, one bit per triangle of the
 // leaf children that were hit}.
@@ -154,9 +170,9 @@ RTC_HD void bvh_node_hits(const float4* __restrict__ nodes, const float4* top, u
 #endif
         for (int j = 0; j < 4; ++j) {
             const int sh = 8 * j;
-            const float t0x = bvh_fma((float)((nearx >> sh) & 0xFFu), sx, bx), t1x = bvh_fma((float)((farx >> sh) & 0xFFu), sx, bx);
-            const float t0y = bvh_fma((float)((neary >> sh) & 0xFFu), sy, by), t1y = bvh_fma((float)((fary >> sh) & 0xFFu), sy, by);
-            const float t0z = bvh_fma((float)((nearz >> sh) & 0xFFu), sz, bz), t1z = bvh_fma((float)((farz >> sh) & 0xFFu), sz, bz);
+            const float t0x = bvh_fma(bvh_byte_f(nearx, j, false), sx, bx), t1x = bvh_fma(bvh_byte_f(farx, j, true), sx, bx);
+            const float t0y = bvh_fma(bvh_byte_f(neary, j, false), sy, by), t1y = bvh_fma(bvh_byte_f(fary, j, true), sy, by);
+            const float t0z = bvh_fma(bvh_byte_f(nearz, j, false), sz, bz), t1z = bvh_fma(bvh_byte_f(farz, j, true), sz, bz);
             const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
             const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (t0 <= t1) hitmask |= ((child_bits4 >> sh) & 0xFFu) << ((bit_index4 >> sh) & 0xFFu);
