@@ -218,13 +218,13 @@ def roofline(name, accel_key, cs, trace_ms, trace_launches, kern_ms, algo_bytes,
         ncu_ms = c.get("per_launch", {}).get("ncu_ms") or []
         if c.get("dram_bytes_per_launch") and ncu_ms:
             cap_ms = sum(ncu_ms) / len(ncu_ms)
-            # the captured launches are the 6 GiB-stage batches (1/6.4 of a frame); a timed launch traces the whole frame's bounce:
-            # the capture's bytes are scaled by the ratio of the launch durations to give bytes per TIMED launch
+            # the capture's bytes are scaled by the ratio of the launch durations to give bytes per TIMED launch: ~1 for a capture
+            # of one-batch launches (BVH, profiles/r2z_*), ~6.4 where the captured launches were the 6 GiB-stage batches (grid)
             out["traffic"] = int(c["dram_bytes_per_launch"] * avg_ms / cap_ms)
             gbs = c["dram_bytes_per_launch"] / (cap_ms * 1e-3) / 1e9
             out["dram"] = {"achieved": round(gbs, 1), "frac": round(gbs / peak, 4), "unit": "GB/s",
-                           "note": "measured dram__bytes_read+write of the captured launches / their own duration under ncu (%.2f ms, a 6 GiB-stage batch); "
-                                   "traffic = those bytes scaled to the duration of a timed launch" % cap_ms}
+                           "note": "measured dram__bytes_read+write of the captured launches / their own duration under ncu (%.2f ms per launch); "
+                                   "traffic = those bytes scaled to the duration of a timed launch (x%.2f)" % (cap_ms, avg_ms / cap_ms)}
         out["issue"] = {k: c[k] for k in ("issue_active", "lanes_per_inst", "useful_lane_issue", "l1_throughput", "l2_throughput",
                                           "warps_active", "registers") if k in c}
         out["issue"]["source"] = c.get("source")

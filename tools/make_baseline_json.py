@@ -45,10 +45,10 @@ def main():
     r1 = old.get("round1_runs") or old.get("runs", [])
     runs = []
     for rel, label in [
-        ("profiles/r2_final_bench.json", "cfg3 1 GPU, default bench line (RTC_ACCEL_BVH)"),
-        ("profiles/r2_final_bench_grid.json", "cfg3 1 GPU, --accel grid (the reference's structure, bit-exact)"),
+        ("profiles/r2z_bench.json", "cfg3 1 GPU, default bench line (RTC_ACCEL_BVH)"),
+        ("profiles/r2z_bench_grid.json", "cfg3 1 GPU, --accel grid (the reference's structure, bit-exact)"),
         ("profiles/r2a_bench_fast.json", "cfg3 1 GPU, grid, --math fast (FMA contraction; round-2 start kernel)"),
-        ("profiles/r2_final_cfg4_bvh.json", "cfg4 scene 1 GPU at 8 spp, BVH"),
+        ("profiles/r2z_cfg4_bvh.json", "cfg4 scene 1 GPU at 8 spp, BVH"),
         ("profiles/r2a_cfg4_128x128x128.json", "cfg4 scene 1 GPU at 8 spp, grid 128^3 (the reference's config.json)"),
         ("profiles/r2a_cfg4_512x128x512.json", "cfg4 scene 1 GPU at 8 spp, grid with tuned grid_resolution 512x128x512 (a config.json key)"),
         ("profiles/r2a_cfg3_256x96x128.json", "cfg3 1 GPU at 16 spp, grid with tuned grid_resolution 256x96x128"),

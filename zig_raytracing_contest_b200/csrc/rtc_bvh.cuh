@@ -211,13 +211,20 @@ RTC_HD void bvh_test_tri(const BvhView& b, const Ray& ray, uint32_t ti, BvhTrav&
     }
 }
 
+// The traversal stack behind put / get: a plain strided array here; k_trace_bvh may keep its first entries in shared memory.
+struct BvhArrayStack {
+    uint2* p; uint32_t stride;
+    RTC_HD void put(uint32_t k, uint2 v) { p[k * stride] = v; }
+    RTC_HD uint2 get(uint32_t k) const { return p[k * stride]; }
+};
+
 // One iteration in two halves, so that the kernel can put the triangle tests of a whole warp into one pool between
 // them. bvh_step_nodes: pop the nearest pending child (or a postponed triangle group) and test its children; returns
 // the triangle group {tri_base, one bit per triangle of the leaves that were hit}. bvh_step_pop: take the next group
 // off the stack when the current one is used up; returns true when the ray is done.
 // nodes counts what the STATS build reports (80-byte node records fetched).
-template <bool STATS>
-RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2* stack, uint32_t stride, uint32_t& nodes,
+template <bool STATS, class Stack>
+RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, Stack& stack, uint32_t& nodes,
                             const float4* top = nullptr, uint32_t ntop = 0u)
 {
     uint2 tg;
@@ -225,7 +232,7 @@ RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2
         const uint32_t hits = s.ng.y;
         const uint32_t bit = 31u - bvh_clz(hits);
         s.ng.y &= ~(1u << bit);
-        if (s.ng.y > 0x00FFFFFFu) { stack[s.sp * stride] = s.ng; s.sp += 1u; }
+        if (s.ng.y > 0x00FFFFFFu) { stack.put(s.sp, s.ng); s.sp += 1u; }
         const uint32_t slot = (bit - 24u) ^ (r.octinv4 & 7u);
         const uint32_t rel = bvh_popc(hits & ~(0xFFFFFFFFu << slot));
         if (STATS) nodes += 1u;
@@ -236,29 +243,31 @@ RTC_HD uint2 bvh_step_nodes(const BvhView& b, const BvhRay& r, BvhTrav& s, uint2
     }
     return tg;
 }
-RTC_HD bool bvh_step_pop(BvhTrav& s, const uint2* stack, uint32_t stride)
+template <class Stack>
+RTC_HD bool bvh_step_pop(BvhTrav& s, const Stack& stack)
 {
     if (s.ng.y <= 0x00FFFFFFu) {
         if (s.sp == 0u) return true;
         s.sp -= 1u;
-        s.ng = stack[s.sp * stride];
+        s.ng = stack.get(s.sp);
     }
     return false;
 }
 
 // The whole iteration for one ray on its own (the host-side checker, tests/native/bvh_check.cu).
 template <bool STATS>
-RTC_HD bool bvh_step(const BvhView& b, const BvhRay& r, const Ray& ray, BvhTrav& s, uint2* stack, uint32_t stride,
+RTC_HD bool bvh_step(const BvhView& b, const BvhRay& r, const Ray& ray, BvhTrav& s, uint2* stack_mem, uint32_t stride,
                      uint32_t& nodes, uint32_t& tests)
 {
-    uint2 tg = bvh_step_nodes<STATS>(b, r, s, stack, stride, nodes);
+    BvhArrayStack stack{ stack_mem, stride };
+    uint2 tg = bvh_step_nodes<STATS>(b, r, s, stack, nodes);
     while (tg.y != 0u) {
         const uint32_t rel = 31u - bvh_clz(tg.y);
         tg.y &= ~(1u << rel);
         if (STATS) tests += 1u;
         bvh_test_tri(b, ray, tg.x + rel, s);
     }
-    return bvh_step_pop(s, stack, stride);
+    return bvh_step_pop(s, stack);
 }
 
 }  // namespace rtc

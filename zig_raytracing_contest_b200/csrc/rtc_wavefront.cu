@@ -48,6 +48,26 @@ static constexpr int kMaxStep = RTC_KMAXSTEP;        // DDA steps a lane may tak
 #define RTC_CHUNK 64
 #endif
 static constexpr uint32_t kChunk = RTC_CHUNK;        // queue entries a warp reserves per atomic
+// A warp that reserves a chunk of its input queue asks L2 for the chunk's lines: the queue was written by the previous
+// kernel (6 GB per bounce of cfg3) and comes from DRAM, and the chunk is consumed a few entries at a time over many
+// rounds — every refill but the first then finds its entries in L2. +0.4 % on cfg3 (profiles/r2z_ab_stack.txt).
+#ifndef RTC_QUEUE_PREFETCH
+#define RTC_QUEUE_PREFETCH 1
+#endif
+template <uint32_t PLANES>
+__device__ __forceinline__ void queue_prefetch_chunk(const RayQueue& q, uint32_t base, uint32_t end, uint32_t lane)
+{
+#if RTC_QUEUE_PREFETCH
+    // 8 entries of 16 B per 128-byte line: lane -> (plane, line of the chunk)
+    constexpr uint32_t kLines = kChunk / 8u;
+    static_assert(PLANES * kLines <= 32u, "one prefetch per lane covers the chunk");
+    if (lane < PLANES * kLines) {
+        const uint32_t plane = lane / kLines, e = base + 8u * (lane % kLines);
+        const float4* a = plane == 0u ? q.a0 : plane == 1u ? q.a1 : plane == 2u ? q.a2 : q.a3;
+        if (e < end) asm volatile("prefetch.global.L2 [%0];" :: "l"(a + e));
+    }
+#endif
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // Ray queue entry (64 B, SoA over four float4 arrays): the ray and its DDA set-up.
@@ -290,7 +310,7 @@ k_trace(const __grid_constant__ DevScene sc, const RayQueue q, const uint32_t* _
                 if (lane == 0) base = atomicAdd(head_ptr, kChunk);
                 base = __shfl_sync(kFull, base, 0);
                 if (base >= n) { exhausted = true; next = end = 0; }
-                else { next = base; end = base + kChunk < n ? base + kChunk : n; }
+                else { next = base; end = base + kChunk < n ? base + kChunk : n; queue_prefetch_chunk<4u>(q, next, end, lane); }
             }
             const uint32_t avail = end - next, want = __popc(idle);
             const uint32_t take = want < avail ? want : avail;
@@ -410,6 +430,21 @@ static constexpr uint32_t kBvhTop = RTC_BVH_TOP;
 #endif
 static constexpr uint32_t kBvhDirect = RTC_BVH_DIRECT;        // rounds whose busiest lane has at most this many triangles skip the pool
 
+// EXPERIMENT, off. RTC_BVH_SSTACK = K > 0: the first K stack entries of every lane in shared memory (lane-contiguous,
+// conflict-free), deeper ones in local memory — the pops are long-scoreboard stalls (4.7 % of the samples: their L1 lines
+// are evicted between push and pop), but K = 2 / 4 / 8 measured -1.1 % / -0.25 % / -0.55 % (profiles/r2z_ab_stack.txt):
+// the branch per access and the L1 capacity given to shared memory cost what the faster pops give.
+#ifndef RTC_BVH_SSTACK
+#define RTC_BVH_SSTACK 0
+#endif
+static constexpr uint32_t kBvhSStack = RTC_BVH_SSTACK;
+struct BvhHybridStack {
+    uint2* sh;                 // entry k of this lane at sh[k * kTraceThreads]
+    uint2* lo;                 // local memory, entries kBvhSStack..
+    __device__ __forceinline__ void put(uint32_t k, uint2 v) { if (k < kBvhSStack) sh[k * kTraceThreads] = v; else lo[k - kBvhSStack] = v; }
+    __device__ __forceinline__ uint2 get(uint32_t k) const { return k < kBvhSStack ? sh[k * kTraceThreads] : lo[k - kBvhSStack]; }
+};
+
 struct BvhShared {
     float4 ro[32];                      // per lane: ray origin
     float4 rd[32];                      // per lane: ray direction
@@ -442,7 +477,13 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
     BvhRay br; BvhTrav s;
     br.ox = br.oy = br.oz = 0.0f; br.ix = br.iy = br.iz = 1.0f; br.octinv4 = 0u;
     bvh_trav_begin(s);
-    uint2 stack[kBvhStack];
+    uint2 stack_mem[kBvhStack];
+#if RTC_BVH_SSTACK
+    __shared__ uint2 s_stack[kBvhSStack * kTraceThreads];
+    BvhHybridStack stack{ s_stack + threadIdx.x, stack_mem };
+#else
+    BvhArrayStack stack{ stack_mem, 1u };
+#endif
     for (;;) {
         // ---- refill: idle lanes take the next rays of the queue ----
         const uint32_t idle = __ballot_sync(kFull, !alive);
@@ -452,7 +493,10 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
                 if (lane == 0) base = atomicAdd(head_ptr, kChunk);
                 base = __shfl_sync(kFull, base, 0);
                 if (base >= n) { exhausted = true; next = end = 0; }
-                else { next = base; end = base + kChunk < n ? base + kChunk : n; }
+                else {
+                    next = base; end = base + kChunk < n ? base + kChunk : n;
+                    queue_prefetch_chunk<3u>(q, next, end, lane);
+                }
             }
             const uint32_t avail = end - next, want = __popc(idle);
             const uint32_t take = want < avail ? want : avail;
@@ -473,7 +517,7 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
         }
         // ---- A: one node per live lane ----
         uint2 tg = make_uint2(0u, 0u);
-        if (alive) tg = bvh_step_nodes<STATS>(bv, br, s, stack, 1u, cn.cells, s_top, ntop);
+        if (alive) tg = bvh_step_nodes<STATS>(bv, br, s, stack, cn.cells, s_top, ntop);
         // ---- B: pooled triangle tests ----
         const uint32_t cnt = __popc(tg.y);
         if (STATS) cn.tris += cnt;
@@ -552,7 +596,7 @@ k_trace_bvh(const BvhView bv, const RayQueue q, const uint32_t* __restrict__ cou
             __syncwarp();
         }
         // ---- C (second half): next group, or the ray is done ----
-        if (alive && bvh_step_pop(s, stack, 1u)) {
+        if (alive && bvh_step_pop(s, stack)) {
             // the whole hit travels to the shading kernel: t, u, v and the source triangle (16 B; no triangle fetch there)
             const float2 uv = s.best_tri != kMiss ? ws.buv[lane] : make_float2(0.0f, 0.0f);
             __stcs(hits + qi, make_float4(s.best_t, uv.x, uv.y, __uint_as_float(s.best_tri)));
