@@ -641,6 +641,15 @@ __device__ __forceinline__ void interp_uv(const TriData& d, float u, float v, fl
 #define RTC_SHADE_MINB 4
 #endif
 static constexpr uint32_t kMatSmem = 32;             // material tables up to this size are staged in shared memory
+// Rounds ahead for which a thread asks L2 for its queue entry and hit record (0 = off): the chain of dependent loads of one
+// ray starts with three DRAM reads (the queue was streamed out by the previous kernels) and nothing overlaps them but the
+// other warps of the SM. Distance 1 / 2 / 4: +1.0 % / +1.1 % / +0.8 % on cfg3 (profiles/r2z_ab_shade_prefetch.txt).
+#ifndef RTC_SHADE_PREFETCH
+#define RTC_SHADE_PREFETCH 2
+#endif
+// Measured and dropped: reading the NEXT round's hit id one round ahead and asking its triangle record into L1 at the end of
+// the round (the second link of the chain): -0.6 % with the BVH, -1.2 % with the grid (profiles/r2z_ab_shade_tri.txt): the extra
+// live register spills and the extra load costs more than the L2 latency it hides.
 
 template <bool PRIMARY, bool BVH>
 __global__ void __launch_bounds__(kThreads, RTC_SHADE_MINB)
@@ -667,6 +676,17 @@ k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevCamera c
         const uint32_t i = it * stride + blockIdx.x * kThreads + threadIdx.x;
         bool push = false;
         QueuedRay e;
+#if RTC_SHADE_PREFETCH
+        {
+            const uint32_t ip = i + RTC_SHADE_PREFETCH * stride;
+            if (ip < n) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(qin.a0 + ip));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(qin.a1 + ip));
+                if (BVH) asm volatile("prefetch.global.L2 [%0];" :: "l"(qin.a3 + ip));
+                else asm volatile("prefetch.global.L2 [%0];" :: "l"(ws.hits + ip));
+            }
+        }
+#endif
         if (i < n) {
             const float4 a0 = __ldcs(qin.a0 + i), a1 = __ldcs(qin.a1 + i);
             // grid: {t bits, baked triangle}; BVH: {t, u, v, source id} in the a3 plane of the input queue
