@@ -437,6 +437,9 @@ static constexpr uint32_t kBvhDirect = RTC_BVH_DIRECT;        // rounds whose bu
 #ifndef RTC_BVH_SSTACK
 #define RTC_BVH_SSTACK 0
 #endif
+// Measured and dropped: asking L1 (prefetch.global.L1) for the node a lane visits next as soon as it is known (after the node test /
+// after a pop), or for the first triangle of a group ahead of the pooled tests: -23 % / -55 % / -2 % (profiles/r2z_ab_node_prefetch.txt).
+// Every lane's prefetch is one more L1 tag lookup per sector, and the L1 tag rate is the kernel's second roof (l1tex 0.73).
 static constexpr uint32_t kBvhSStack = RTC_BVH_SSTACK;
 struct BvhHybridStack {
     uint2* sh;                 // entry k of this lane at sh[k * kTraceThreads]
