@@ -52,7 +52,8 @@ def main():
         ("profiles/r2a_cfg4_128x128x128.json", "cfg4 scene 1 GPU at 8 spp, grid 128^3 (the reference's config.json)"),
         ("profiles/r2a_cfg4_512x128x512.json", "cfg4 scene 1 GPU at 8 spp, grid with tuned grid_resolution 512x128x512 (a config.json key)"),
         ("profiles/r2a_cfg3_256x96x128.json", "cfg3 1 GPU at 16 spp, grid with tuned grid_resolution 256x96x128"),
-        ("profiles/r2w_bench_n2.json", "cfg3 2 GPUs strong, strips over rtc_render_sharded (NCCL send/recv)"),
+        ("profiles/r2z_bench_n2.json", "cfg3 2 GPUs strong, strips over rtc_render_sharded (NCCL send/recv), final kernels"),
+        ("profiles/r2z_bench_n4.json", "cfg3 4 GPUs strong, strips over rtc_render_sharded, final kernels"),
         ("profiles/r2w_bench_n2_samples.json", "cfg3 2 GPUs strong, sample ranges over rtc_render_sharded (ncclReduce of rgb)"),
         ("profiles/r2w_inproc2.json", "cfg3 2 GPUs strong, ONE process: rtc_render(num_gpus=2), host clock incl. D2H"),
         ("profiles/r2_n8_cfg3_strips.json", "cfg3 8 GPUs strong, strips"),
