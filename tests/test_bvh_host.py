@@ -151,3 +151,22 @@ def test_bvh_random_soup_many_rays(checker):
     assert bad == 0
     bad1, tri1, t1, *_ = run(checker, tris, rays, threads=8)                 # the tree may differ, the answers may not
     assert bad1 == 0 and np.array_equal(tri, tri1) and np.array_equal(t.view(np.uint32), t1.view(np.uint32))
+
+
+def test_bvh_long_ranges_split_by_several_threads(checker):
+    """Ranges of 2^17 triangles or more are binned and partitioned by several threads (stable, out of place): the answers
+    equal brute force and the TREE — node count, depth, node visits and triangle tests of the same rays — is the same
+    whatever the number of threads."""
+    spec = scenes.terrain(300_000)
+    tris = tri_records(spec.positions)
+    assert len(tris) >= (1 << 17) * 2
+    rays = camera_rays(spec, 40, 400, 7)
+    out = {}
+    for threads in (1, 3, 8):
+        bad, tri, t, btri, bt, stats = run(checker, tris, rays, threads=threads)
+        assert bad == 0
+        out[threads] = (tri, t, tuple(int(x) for x in stats[:4]))
+    assert (out[1][0] >= 0).sum() > 100
+    for threads in (3, 8):
+        assert np.array_equal(out[threads][0], out[1][0]) and np.array_equal(out[threads][1].view(np.uint32), out[1][1].view(np.uint32))
+        assert out[threads][2] == out[1][2]
