@@ -1,5 +1,7 @@
-// scratch: times rtc_bvh_build_host on a synthetic terrain-like soup
-#include "../zig_raytracing_contest_b200/csrc/rtc_bvh_host.h"
+// scratch: times rtc_bvh_build_host on a synthetic terrain-like soup (2 * side^2 triangles), host only:
+//   g++ -O3 -std=c++17 -o /tmp/bvhtime tools/scratch/bvhtime.cpp zig_raytracing_contest_b200/csrc/rtc_bvh_build.cpp -lpthread
+//   RTC_TRACE_BVH=1 /tmp/bvhtime 1581 16        (side, threads; profiles/r2zz_bvhtime_*.txt)
+#include "../../zig_raytracing_contest_b200/csrc/rtc_bvh_host.h"
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
